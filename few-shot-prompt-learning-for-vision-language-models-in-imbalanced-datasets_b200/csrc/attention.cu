@@ -1,0 +1,48 @@
+// C-ABI entry points of the attention core; picks the tensor-core kernels (bf16 fast mode) or the
+// CUDA-core kernels (fp32 validation mode).  See include/psrc_b200.h for the contract.
+#include "common.cuh"
+
+namespace psrc {
+int attn_fwd_simt(const void* qkv, void* out, float* lse, int dtype, int n_seq, int L, int H, int causal,
+                  cudaStream_t s);
+int attn_bwd_simt(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int dtype,
+                  int n_seq, int L, int H, int causal, cudaStream_t s);
+int attn_fwd_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s);
+int attn_bwd_mma(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int n_seq,
+                 int L, int H, int causal, cudaStream_t s);
+}  // namespace psrc
+
+using namespace psrc;
+
+static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, int n_seq, int L, int H,
+                             int causal, int backend, psrc_stream_t stream) {
+  PSRC_CHECK_ARG(qkv && out && lse, "psrc_attn_fwd: null pointer");
+  PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && H > 0, "psrc_attn_fwd: bad shape n_seq=%d L=%d H=%d", n_seq, L, H);
+  PSRC_CHECK_ARG(dtype == PSRC_F32 || dtype == PSRC_BF16, "psrc_attn_fwd: bad dtype");
+  PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_fwd: n_seq=%d exceeds the grid limit 65535", n_seq);
+  if (n_seq == 0) return PSRC_OK;
+  if (backend == 0) backend = (dtype == PSRC_BF16 && al16(qkv) && al16(out)) ? 2 : 1;
+  if (backend == 2) {
+    PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out), "psrc_attn_fwd: tensor-core backend needs aligned bf16");
+    return attn_fwd_mma(qkv, out, lse, n_seq, L, H, causal, as_stream(stream));
+  }
+  return attn_fwd_simt(qkv, out, lse, dtype, n_seq, L, H, causal, as_stream(stream));
+}
+
+extern "C" int psrc_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                             int dtype, int n_seq, int L, int H, int causal, int backend, psrc_stream_t stream) {
+  PSRC_CHECK_ARG(qkv && out && dout && lse && dqkv, "psrc_attn_bwd: null pointer");
+  PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && H > 0, "psrc_attn_bwd: bad shape n_seq=%d L=%d H=%d", n_seq, L, H);
+  PSRC_CHECK_ARG(dtype == PSRC_F32 || dtype == PSRC_BF16, "psrc_attn_bwd: bad dtype");
+  PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_bwd: n_seq=%d exceeds the grid limit 65535", n_seq);
+  if (n_seq == 0) return PSRC_OK;
+  const bool ok16 = al16(qkv) && al16(out) && al16(dout) && al16(dqkv);
+  if (backend == 0) backend = (dtype == PSRC_BF16 && ok16) ? 2 : 1;
+  if (backend == 2) {
+    PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16, "psrc_attn_bwd: tensor-core backend needs aligned bf16");
+    return attn_bwd_mma(qkv, out, dout, lse, dqkv, n_seq, L, H, causal, as_stream(stream));
+  }
+  return attn_bwd_simt(qkv, out, dout, lse, dqkv, dtype, n_seq, L, H, causal, as_stream(stream));
+}
