@@ -1,0 +1,175 @@
+"""Thin tensor-level wrappers over the C ABI (one function per kernel family).
+
+PyTorch only provides device memory and the stream here; all arithmetic runs in the
+hand-written sm_100a kernels of ``csrc/``.  Shapes follow ``include/psrc_b200.h``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import cabi
+from .cabi import (ACT_NONE, ACT_QUICKGELU, ACT_QUICKGELU_GRAD, BF16, F32, GEMM_AUTO, GEMM_SIMT,
+                   GEMM_TCGEN05, dt, ptr)
+
+LN_EPS = 1e-5  # nn.LayerNorm default used by PromptSRC/clip/model.py:153
+
+
+def _ld(t: torch.Tensor) -> int:
+    assert t.dim() == 2 and t.stride(1) == 1, "row-major 2-D tensor expected"
+    return t.stride(0)
+
+
+def gemm(a, w, out, bias=None, act=ACT_NONE, aux=None, residual=None, out2=None, alpha=1.0,
+         backend=GEMM_AUTO):
+    """out[M,N] = act(alpha * a[M,K] @ w[N,K]^T + bias) + residual   (see psrc_gemm)."""
+    M, K = a.shape
+    N = w.shape[0]
+    assert w.shape[1] == K and out.shape == (M, N) and a.dtype == w.dtype
+    g = cabi.GemmArgs()
+    g.M, g.N, g.K, g.ab_dtype = M, N, K, dt(a)
+    g.A, g.lda, g.W, g.ldw = ptr(a), _ld(a), ptr(w), _ld(w)
+    g.bias = ptr(bias)
+    g.act = act
+    if aux is not None:
+        g.aux, g.ldaux, g.aux_dtype = ptr(aux), _ld(aux), dt(aux)
+    if residual is not None:
+        assert residual.dtype == torch.float32
+        g.residual, g.ldres = ptr(residual), _ld(residual)
+    g.out, g.ldo, g.out_dtype = ptr(out), _ld(out), dt(out)
+    if out2 is not None:
+        g.out2, g.ldo2, g.out2_dtype = ptr(out2), _ld(out2), dt(out2)
+    g.alpha, g.backend = float(alpha), backend
+    cabi.check(cabi.load().psrc_gemm(C.byref(g), cabi.stream()), "psrc_gemm")
+    return out
+
+
+def gemm_f32_strided(M, N, K, a, a_sm, a_sk, b, b_sn, b_sk, c, alpha=1.0, beta=0.0):
+    """c[M,N] = alpha * sum_k a(m,k) b(n,k) + beta * c  (fp32, element strides)."""
+    assert a.dtype == b.dtype == c.dtype == torch.float32
+    cabi.check(cabi.load().psrc_gemm_f32_strided(M, N, K, ptr(a), a_sm, a_sk, ptr(b), b_sn, b_sk, ptr(c),
+                                                 _ld(c), float(alpha), float(beta), cabi.stream()),
+               "psrc_gemm_f32_strided")
+    return c
+
+
+def layernorm_fwd(x, gamma, beta, y, mean=None, rstd=None, eps=LN_EPS):
+    rows, D = x.shape
+    cabi.check(cabi.load().psrc_layernorm_fwd(ptr(x), ptr(gamma), ptr(beta), ptr(y), dt(y), ptr(mean), ptr(rstd),
+                                              rows, D, eps, cabi.stream()), "psrc_layernorm_fwd")
+    return y
+
+
+def layernorm_bwd(dy, x, gamma, mean, rstd, dx_out, dx_in=None, dx_act=None):
+    rows, D = x.shape
+    cabi.check(cabi.load().psrc_layernorm_bwd(ptr(dy), dt(dy), ptr(x), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx_in),
+                                              ptr(dx_out), ptr(dx_act), dt(dx_act) if dx_act is not None else F32,
+                                              rows, D, cabi.stream()), "psrc_layernorm_bwd")
+    return dx_out
+
+
+def attn_fwd(qkv, out, lse, n_seq, L, H, causal, backend=0):
+    cabi.check(cabi.load().psrc_attn_fwd(ptr(qkv), ptr(out), ptr(lse), dt(qkv), n_seq, L, H, int(causal), backend,
+                                         cabi.stream()), "psrc_attn_fwd")
+    return out
+
+
+def attn_bwd(qkv, out, dout, lse, dqkv, n_seq, L, H, causal, backend=0):
+    cabi.check(cabi.load().psrc_attn_bwd(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), dt(qkv), n_seq, L, H,
+                                         int(causal), backend, cabi.stream()), "psrc_attn_bwd")
+    return dqkv
+
+
+def im2col_patches(image, patches, R, P):
+    B = image.shape[0]
+    cabi.check(cabi.load().psrc_im2col_patches(ptr(image), ptr(patches), dt(patches), B, R, P, cabi.stream()),
+               "psrc_im2col_patches")
+    return patches
+
+
+def assemble_vision_tokens(pe, cls, pos, vpt, ln_g, ln_b, x, B, n_patches, n_ctx, D, eps=LN_EPS):
+    cabi.check(cabi.load().psrc_assemble_vision_tokens(ptr(pe), dt(pe), ptr(cls), ptr(pos), ptr(vpt), ptr(ln_g),
+                                                       ptr(ln_b), ptr(x), B, n_patches, n_ctx, D, eps,
+                                                       cabi.stream()), "psrc_assemble_vision_tokens")
+    return x
+
+
+def assemble_text_prompts(prefix, suffix, ctx, pos, x, C_, L, n_ctx, D, ctx_per_class=False, ctx_bias=None,
+                          n_groups=1):
+    suffix_len = suffix.shape[1]
+    cabi.check(cabi.load().psrc_assemble_text_prompts(ptr(prefix), ptr(suffix), suffix_len, ptr(ctx),
+                                                      int(ctx_per_class), ptr(ctx_bias), n_groups, ptr(pos), ptr(x),
+                                                      C_, L, n_ctx, D, cabi.stream()), "psrc_assemble_text_prompts")
+    return x
+
+
+def insert_prompt(x, prompt, n_seq, L, start, n_ctx, D, round_fp16=True):
+    cabi.check(cabi.load().psrc_insert_prompt(ptr(x), ptr(prompt), n_seq, L, start, n_ctx, D, int(round_fp16),
+                                              cabi.stream()), "psrc_insert_prompt")
+    return x
+
+
+def prompt_grad(dx, grad, n_seq, L, start, n_ctx, D, zero_rows=True, accumulate=False):
+    cabi.check(cabi.load().psrc_prompt_grad(ptr(dx), ptr(grad), n_seq, L, start, n_ctx, D, int(zero_rows),
+                                            int(accumulate), cabi.stream()), "psrc_prompt_grad")
+    return grad
+
+
+def gather_ln_fwd(x, idx, gamma, beta, y, mean, rstd, n_seq, L, D, eps=LN_EPS):
+    cabi.check(cabi.load().psrc_gather_ln_fwd(ptr(x), ptr(idx), ptr(gamma), ptr(beta), ptr(y), dt(y), ptr(mean),
+                                              ptr(rstd), n_seq, L, D, eps, cabi.stream()), "psrc_gather_ln_fwd")
+    return y
+
+
+def gather_ln_bwd(dy, x, idx, gamma, mean, rstd, dx, n_seq, L, D):
+    cabi.check(cabi.load().psrc_gather_ln_bwd(ptr(dy), dt(dy), ptr(x), ptr(idx), ptr(gamma), ptr(mean), ptr(rstd),
+                                              ptr(dx), n_seq, L, D, cabi.stream()), "psrc_gather_ln_bwd")
+    return dx
+
+
+def l2norm_fwd(x, y, inv_norm):
+    rows, D = x.shape
+    cabi.check(cabi.load().psrc_l2norm_fwd(ptr(x), ptr(y), ptr(inv_norm), rows, D, cabi.stream()), "psrc_l2norm_fwd")
+    return y
+
+
+def l2norm_bwd(dy, y, inv_norm, dx):
+    rows, D = y.shape
+    cabi.check(cabi.load().psrc_l2norm_bwd(ptr(dy), ptr(y), ptr(inv_norm), ptr(dx), rows, D, cabi.stream()),
+               "psrc_l2norm_bwd")
+    return dx
+
+
+def loss_fwd_bwd(logits, labels, d_logits, losses, scratch, zs_logits=None, focal_alpha=None, focal_gamma=2.0,
+                 t_hat=None, t_zs=None, d_that=None, f_hat=None, f_zs=None, d_fhat=None, w_kl=1.0, w_text=25.0,
+                 w_image=10.0, B_global=None, Ct_global=None):
+    B, Cn = logits.shape
+    a = cabi.LossArgs()
+    a.B, a.C = B, Cn
+    a.E = (t_hat.shape[1] if t_hat is not None else (f_hat.shape[1] if f_hat is not None else 0))
+    a.Ct = t_hat.shape[0] if t_hat is not None else 0
+    a.B_global = B_global or B
+    a.Ct_global = Ct_global or a.Ct
+    assert labels.dtype == torch.int32
+    assert scratch.numel() >= 4 * B + 2 * 296
+    a.logits, a.zs_logits, a.labels = ptr(logits), ptr(zs_logits), ptr(labels)
+    a.focal_alpha, a.focal_gamma = ptr(focal_alpha), float(focal_gamma)
+    a.t_hat, a.t_zs, a.f_hat, a.f_zs = ptr(t_hat), ptr(t_zs), ptr(f_hat), ptr(f_zs)
+    a.w_kl, a.w_text, a.w_image = float(w_kl), float(w_text), float(w_image)
+    a.d_logits, a.d_that, a.d_fhat = ptr(d_logits), ptr(d_that), ptr(d_fhat)
+    a.losses, a.row_scratch = ptr(losses), ptr(scratch)
+    cabi.check(cabi.load().psrc_loss_fwd_bwd(C.byref(a), cabi.stream()), "psrc_loss_fwd_bwd")
+    return losses
+
+
+def sgd_step(p, g, buf, lr_dev, momentum, dampening, weight_decay, nesterov, first_step):
+    cabi.check(cabi.load().psrc_sgd_step(ptr(p), ptr(g), ptr(buf), ptr(lr_dev), momentum, dampening, weight_decay,
+                                         int(nesterov), int(first_step), p.numel(), cabi.stream()), "psrc_sgd_step")
+    return p
+
+
+def cast(src, dst):
+    assert src.numel() == dst.numel() and src.is_contiguous() and dst.is_contiguous()
+    cabi.check(cabi.load().psrc_cast(ptr(src), dt(src), ptr(dst), dt(dst), src.numel(), cabi.stream()), "psrc_cast")
+    return dst
