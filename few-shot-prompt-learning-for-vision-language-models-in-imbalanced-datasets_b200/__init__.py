@@ -9,5 +9,6 @@ is not a Python identifier.
 """
 from . import cabi  # noqa: F401
 from . import ops  # noqa: F401
+from . import synthetic  # noqa: F401
 
 __all__ = ["cabi", "ops"]

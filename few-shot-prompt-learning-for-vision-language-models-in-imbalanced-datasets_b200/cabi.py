@@ -63,14 +63,15 @@ SIGNATURES = {
     "psrc_assemble_vision_tokens": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _vp]),
     "psrc_assemble_text_prompts": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp]),
     "psrc_insert_prompt": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
-    "psrc_prompt_grad": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "psrc_prompt_grad": (_i, [_vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "psrc_gather_ln_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _f, _vp]),
-    "psrc_gather_ln_bwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "psrc_gather_ln_bwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "psrc_l2norm_fwd": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "psrc_l2norm_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp]),
     "psrc_loss_fwd_bwd": (_i, [C.POINTER(LossArgs), _vp]),
     "psrc_sgd_step": (_i, [_vp, _vp, _vp, _vp, _f, _f, _f, _i, _i, _i64, _vp]),
     "psrc_cast": (_i, [_vp, _i, _vp, _i, _i64, _vp]),
+    "psrc_axpy": (_i, [_vp, _vp, _f, _i64, _vp]),
 }
 
 _lib = None

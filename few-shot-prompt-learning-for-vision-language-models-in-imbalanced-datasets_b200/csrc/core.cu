@@ -57,6 +57,12 @@ __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, f
   }
 }
 
+__global__ void axpy_kernel(float* __restrict__ y, const float* __restrict__ x, float a, long long n) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) y[i] = fmaf(a, x[i], y[i]);
+}
+
 }  // namespace psrc
 
 using namespace psrc;
@@ -109,6 +115,14 @@ extern "C" int psrc_sgd_step(float* p, const float* g, float* buf, const float* 
   if (n == 0) return PSRC_OK;
   sgd_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(p, g, buf, lr_dev, momentum, dampening,
                                                               weight_decay, nesterov, first_step, n);
+  PSRC_CHECK_LAUNCH();
+  return PSRC_OK;
+}
+
+extern "C" int psrc_axpy(float* y, const float* x, float a, int64_t n, psrc_stream_t stream) {
+  PSRC_CHECK_ARG(y && x && n >= 0, "psrc_axpy: bad arguments");
+  if (n == 0) return PSRC_OK;
+  axpy_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(y, x, a, n);
   PSRC_CHECK_LAUNCH();
   return PSRC_OK;
 }

@@ -121,7 +121,10 @@ ln_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x, const int32
 #pragma unroll
       for (int i = 0; i < NV; ++i) {
         int c = (lane + 32 * i) * 4;
-        if (c < D) store4<float>(o + c, make_float4(0.f, 0.f, 0.f, 0.f));
+        if (c < D) {
+          store4<float>(o + c, make_float4(0.f, 0.f, 0.f, 0.f));
+          if (dx_act) store4<TA>(dx_act + (long long)r * D + c, make_float4(0.f, 0.f, 0.f, 0.f));
+        }
       }
       return;
     }
@@ -267,11 +270,12 @@ extern "C" int psrc_gather_ln_fwd(const float* x, const int32_t* idx, const floa
 
 extern "C" int psrc_gather_ln_bwd(const void* dy, int dy_dtype, const float* x, const int32_t* idx,
                                   const float* gamma, const float* mean, const float* rstd, float* dx,
-                                  int n_seq, int L, int D, psrc_stream_t stream) {
+                                  void* dx_act, int act_dtype, int n_seq, int L, int D,
+                                  psrc_stream_t stream) {
   const int rows = n_seq * L;
   CHECK_LN_COMMON("psrc_gather_ln_bwd");
   PSRC_CHECK_ARG(dy && x && gamma && mean && rstd && dx && L > 0, "psrc_gather_ln_bwd: bad arguments");
   if (rows == 0) return PSRC_OK;
-  return bwd_dispatch(dy, dy_dtype, x, idx, L, gamma, mean, rstd, nullptr, dx, nullptr, PSRC_F32, rows, D,
+  return bwd_dispatch(dy, dy_dtype, x, idx, L, gamma, mean, rstd, nullptr, dx, dx_act, act_dtype, rows, D,
                       as_stream(stream));
 }

@@ -150,8 +150,9 @@ __global__ void insert_prompt_kernel(float* __restrict__ x, const float* __restr
 // grad[j, d4] (+)= sum over sequences of dx[seq, start+j, d4]; block (64, 8): x over d4, y over sequences.
 // Deterministic (fixed summation order), then optionally zeroes the rows it consumed.
 __global__ void __launch_bounds__(512)
-prompt_grad_kernel(float* __restrict__ dx, float* __restrict__ grad, int n_seq, int L, int start, int n_ctx,
-                   int D, int zero_rows, int accumulate) {
+prompt_grad_kernel(float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16, float* __restrict__ dx_f32copy,
+                   float* __restrict__ grad, int n_seq, int L, int start, int n_ctx, int D, int zero_rows,
+                   int accumulate, int round_fp16) {
   __shared__ float4 red[8][64];
   const int d4 = blockIdx.x * 64 + threadIdx.x;
   const int j = blockIdx.y;
@@ -161,8 +162,14 @@ prompt_grad_kernel(float* __restrict__ dx, float* __restrict__ grad, int n_seq, 
     for (int seq = threadIdx.y; seq < n_seq; seq += 8) {
       float4* p = reinterpret_cast<float4*>(dx + ((long long)seq * L + start + j) * D) + d4;
       float4 v = *p;
+      if (round_fp16) v = make_float4(fp16_round(v.x), fp16_round(v.y), fp16_round(v.z), fp16_round(v.w));
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-      if (zero_rows) *p = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (zero_rows) {
+        *p = make_float4(0.f, 0.f, 0.f, 0.f);
+        const long long off = ((long long)seq * L + start + j) * D + (long long)d4 * 4;
+        if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + off) = make_uint2(0u, 0u);
+        if (dx_f32copy) *reinterpret_cast<float4*>(dx_f32copy + off) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
     }
   }
   red[threadIdx.y][threadIdx.x] = s;
@@ -276,14 +283,17 @@ extern "C" int psrc_insert_prompt(float* x, const float* prompt, int n_seq, int 
   return PSRC_OK;
 }
 
-extern "C" int psrc_prompt_grad(float* dx, float* grad, int n_seq, int L, int start, int n_ctx, int D,
-                                int zero_rows, int accumulate, psrc_stream_t stream) {
+extern "C" int psrc_prompt_grad(float* dx, void* dx_act, int act_dtype, float* grad, int n_seq, int L, int start,
+                                int n_ctx, int D, int zero_rows, int accumulate, int round_fp16,
+                                psrc_stream_t stream) {
   PSRC_CHECK_ARG(dx && grad && D > 0 && D % 4 == 0 && start >= 0 && n_ctx >= 0 && start + n_ctx <= L && n_seq >= 0,
                  "psrc_prompt_grad: bad arguments");
   if (n_ctx == 0) return PSRC_OK;
   dim3 grid((D / 4 + 63) / 64, n_ctx), block(64, 8);
-  prompt_grad_kernel<<<grid, block, 0, as_stream(stream)>>>(dx, grad, n_seq, L, start, n_ctx, D, zero_rows,
-                                                            accumulate);
+  __nv_bfloat16* a16 = (dx_act && act_dtype == PSRC_BF16) ? reinterpret_cast<__nv_bfloat16*>(dx_act) : nullptr;
+  float* a32 = (dx_act && act_dtype == PSRC_F32 && dx_act != (void*)dx) ? reinterpret_cast<float*>(dx_act) : nullptr;
+  prompt_grad_kernel<<<grid, block, 0, as_stream(stream)>>>(dx, a16, a32, grad, n_seq, L, start, n_ctx, D,
+                                                            zero_rows, accumulate, round_fp16);
   PSRC_CHECK_LAUNCH();
   return PSRC_OK;
 }

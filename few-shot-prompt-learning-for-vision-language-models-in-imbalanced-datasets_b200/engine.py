@@ -1,0 +1,142 @@
+"""Host-side orchestration of the prompted-CLIP towers over the C-ABI kernels.
+
+Pure plumbing: this module owns device buffers (torch tensors) and the order of kernel
+launches; every FLOP runs in ``csrc/``.  Buffers are allocated once per (shape, mode) so a
+whole step can be captured into a CUDA graph.
+
+Data layout in HBM: activations are batch-first ``[n_seq * L, D]``; the residual
+stream is fp32; "act" tensors are bf16 (fast mode) or fp32 (validation mode); frozen weights
+are kept as ``W [out, in]`` (forward GEMM operand, K-major) plus ``W^T [in, out]`` (dgrad GEMM
+operand) in act dtype -- they are never given a weight-gradient pass
+(PromptSRC/trainers/promptsrc.py:238-247).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from .ops import ACT_QUICKGELU, ACT_QUICKGELU_GRAD
+
+ACT_DTYPES = {"bf16": torch.bfloat16, "fp32": torch.float32}
+
+
+def _dev(t, device, dtype=torch.float32):
+    return t.detach().to(device=device, dtype=dtype).contiguous()
+
+
+class BlockWeights:
+    """One ResidualAttentionBlock (clip/model.py:167-188) in kernel layout."""
+
+    def __init__(self, sd, p, device, act, need_backward):
+        f = lambda k: _dev(sd[p + k], device)            # noqa: E731  fp32 vectors
+        a = lambda k: _dev(sd[p + k], device, act)       # noqa: E731  GEMM operands
+        self.ln1_g, self.ln1_b = f("ln_1.weight"), f("ln_1.bias")
+        self.ln2_g, self.ln2_b = f("ln_2.weight"), f("ln_2.bias")
+        self.wqkv, self.bqkv = a("attn.in_proj_weight"), f("attn.in_proj_bias")
+        self.wo, self.bo = a("attn.out_proj.weight"), f("attn.out_proj.bias")
+        self.w1, self.b1 = a("mlp.c_fc.weight"), f("mlp.c_fc.bias")
+        self.w2, self.b2 = a("mlp.c_proj.weight"), f("mlp.c_proj.bias")
+        if need_backward:
+            t = lambda k: _dev(sd[p + k].t(), device, act)  # noqa: E731
+            self.wqkv_t, self.wo_t = t("attn.in_proj_weight"), t("attn.out_proj.weight")
+            self.w1_t, self.w2_t = t("mlp.c_fc.weight"), t("mlp.c_proj.weight")
+
+
+class TowerWeights:
+    def __init__(self, sd, prefix, n_layers, device, act, need_backward):
+        self.blocks = [BlockWeights(sd, f"{prefix}resblocks.{i}.", device, act, need_backward)
+                       for i in range(n_layers)]
+        self.need_backward = need_backward
+
+
+class Tower:
+    """A stack of residual attention blocks over ``n_seq`` sequences of length ``L``.
+
+    prompt_layers: {layer i: (start, n_ctx)} -- rows [start, start+n_ctx) of every sequence are
+    overwritten with that layer's deep prompt before the block runs (clip/model.py:232-252).
+    """
+
+    def __init__(self, weights: TowerWeights, n_seq, L, D, H, causal, act, save, device, prompt_layers=None):
+        self.w, self.n_seq, self.L, self.D, self.H, self.causal = weights, n_seq, L, D, H, causal
+        self.act, self.save, self.device = act, save, device
+        self.prompt_layers = dict(prompt_layers or {})
+        self.nl = len(weights.blocks)
+        M = self.M = n_seq * L
+        e = lambda *s, dt=torch.float32: torch.empty(*s, device=device, dtype=dt)  # noqa: E731
+        n_saved = self.nl if save else 1
+        self.X = [e(M, D) for _ in range(self.nl + 1 if save else 2)]
+        self.X1 = [e(M, D) for _ in range(n_saved)]
+        self.qkv = [e(M, 3 * D, dt=act) for _ in range(n_saved)]
+        self.O = [e(M, D, dt=act) for _ in range(n_saved)]
+        self.lse = [e(n_seq, H, L) for _ in range(n_saved)]
+        self.u = [e(M, 4 * D, dt=act) for _ in range(n_saved)]
+        self.stats = [[e(M) for _ in range(4)] for _ in range(n_saved)]  # mean1, rstd1, mean2, rstd2
+        self.h = e(M, D, dt=act)
+        self.g = e(M, 4 * D, dt=act)
+        if save:
+            assert weights.need_backward
+            self.du = e(M, 4 * D, dt=act)
+            self.dh = e(M, D, dt=act)
+            self.dqkv = e(M, 3 * D, dt=act)
+            self.dx = e(M, D)
+            self.dxa = e(M, D, dt=act) if act != torch.float32 else None
+
+    # -- buffers of layer i
+    def _xin(self, i):
+        return self.X[i] if self.save else self.X[i % 2]
+
+    def _xout(self, i):
+        return self.X[i + 1] if self.save else self.X[(i + 1) % 2]
+
+    @property
+    def x0(self):
+        return self.X[0]
+
+    @property
+    def x_final(self):
+        return self.X[self.nl] if self.save else self.X[self.nl % 2]
+
+    def forward(self, prompts=None):
+        """prompts: {layer i: fp32 [n_ctx, D] tensor}.  Input must already be in ``self.x0``."""
+        n_seq, L, D, H = self.n_seq, self.L, self.D, self.H
+        for i, b in enumerate(self.w.blocks):
+            s = i if self.save else 0
+            x0, x1, x2 = self._xin(i), self.X1[s], self._xout(i)
+            if i in self.prompt_layers:
+                start, n_ctx = self.prompt_layers[i]
+                ops.insert_prompt(x0, prompts[i], n_seq, L, start, n_ctx, D, round_fp16=True)
+            mean1, rstd1, mean2, rstd2 = self.stats[s]
+            ops.layernorm_fwd(x0, b.ln1_g, b.ln1_b, self.h, mean1, rstd1)
+            ops.gemm(self.h, b.wqkv, self.qkv[s], bias=b.bqkv)
+            ops.attn_fwd(self.qkv[s], self.O[s], self.lse[s], n_seq, L, H, self.causal)
+            ops.gemm(self.O[s], b.wo, x1, bias=b.bo, residual=x0)
+            ops.layernorm_fwd(x1, b.ln2_g, b.ln2_b, self.h, mean2, rstd2)
+            ops.gemm(self.h, b.w1, self.g, bias=b.b1, act=ACT_QUICKGELU, out2=self.u[s] if self.save else None)
+            ops.gemm(self.g, b.w2, x2, bias=b.b2, residual=x1)
+        return self.x_final
+
+    def backward(self, prompt_grads=None, stop_at_layer=0):
+        """Input-gradient chain.  ``self.dx`` (fp32) and ``self.dxa`` (act copy; fp32 mode: dx itself)
+        must hold d(loss)/d(x_final).  On return ``self.dx`` holds d(loss)/d(x0) (rows of replaced
+        prompt tokens zeroed) and prompt_grads[i] ([n_ctx, D] fp32) are overwritten."""
+        assert self.save
+        n_seq, L, D, H = self.n_seq, self.L, self.D, self.H
+        dx = self.dx
+        dxa = self.dxa if self.dxa is not None else self.dx
+        for i in range(self.nl - 1, stop_at_layer - 1, -1):
+            b = self.w.blocks[i]
+            mean1, rstd1, mean2, rstd2 = self.stats[i]
+            # MLP branch: x2 = x1 + W2 . gelu(W1 . LN2(x1))
+            ops.gemm(dxa, b.w2_t, self.du, act=ACT_QUICKGELU_GRAD, aux=self.u[i])
+            ops.gemm(self.du, b.w1_t, self.dh)
+            ops.layernorm_bwd(self.dh, self.X1[i], b.ln2_g, mean2, rstd2, dx, dx_in=dx, dx_act=self.dxa)
+            # attention branch: x1 = x0 + Wo . attn(Wqkv . LN1(x0))
+            ops.gemm(dxa, b.wo_t, self.dh)
+            ops.attn_bwd(self.qkv[i], self.O[i], self.dh, self.lse[i], self.dqkv, n_seq, L, H, self.causal)
+            ops.gemm(self.dqkv, b.wqkv_t, self.dh)
+            ops.layernorm_bwd(self.dh, self.X[i], b.ln1_g, mean1, rstd1, dx, dx_in=dx, dx_act=self.dxa)
+            if i in self.prompt_layers:
+                start, n_ctx = self.prompt_layers[i]
+                ops.prompt_grad(dx, prompt_grads[i], n_seq, L, start, n_ctx, D, zero_rows=True,
+                                dx_act=self.dxa, round_fp16=True)
+        return dx

@@ -110,9 +110,11 @@ def insert_prompt(x, prompt, n_seq, L, start, n_ctx, D, round_fp16=True):
     return x
 
 
-def prompt_grad(dx, grad, n_seq, L, start, n_ctx, D, zero_rows=True, accumulate=False):
-    cabi.check(cabi.load().psrc_prompt_grad(ptr(dx), ptr(grad), n_seq, L, start, n_ctx, D, int(zero_rows),
-                                            int(accumulate), cabi.stream()), "psrc_prompt_grad")
+def prompt_grad(dx, grad, n_seq, L, start, n_ctx, D, zero_rows=True, accumulate=False, dx_act=None,
+                round_fp16=False):
+    cabi.check(cabi.load().psrc_prompt_grad(ptr(dx), ptr(dx_act), dt(dx_act) if dx_act is not None else F32,
+                                            ptr(grad), n_seq, L, start, n_ctx, D, int(zero_rows),
+                                            int(accumulate), int(round_fp16), cabi.stream()), "psrc_prompt_grad")
     return grad
 
 
@@ -122,9 +124,10 @@ def gather_ln_fwd(x, idx, gamma, beta, y, mean, rstd, n_seq, L, D, eps=LN_EPS):
     return y
 
 
-def gather_ln_bwd(dy, x, idx, gamma, mean, rstd, dx, n_seq, L, D):
+def gather_ln_bwd(dy, x, idx, gamma, mean, rstd, dx, n_seq, L, D, dx_act=None):
     cabi.check(cabi.load().psrc_gather_ln_bwd(ptr(dy), dt(dy), ptr(x), ptr(idx), ptr(gamma), ptr(mean), ptr(rstd),
-                                              ptr(dx), n_seq, L, D, cabi.stream()), "psrc_gather_ln_bwd")
+                                              ptr(dx), ptr(dx_act), dt(dx_act) if dx_act is not None else F32,
+                                              n_seq, L, D, cabi.stream()), "psrc_gather_ln_bwd")
     return dx
 
 
@@ -173,3 +176,9 @@ def cast(src, dst):
     assert src.numel() == dst.numel() and src.is_contiguous() and dst.is_contiguous()
     cabi.check(cabi.load().psrc_cast(ptr(src), dt(src), ptr(dst), dt(dst), src.numel(), cabi.stream()), "psrc_cast")
     return dst
+
+
+def axpy(y, x, a=1.0):
+    assert y.dtype == x.dtype == torch.float32 and y.numel() == x.numel() and y.is_contiguous() and x.is_contiguous()
+    cabi.check(cabi.load().psrc_axpy(ptr(y), ptr(x), float(a), y.numel(), cabi.stream()), "psrc_axpy")
+    return y

@@ -148,10 +148,15 @@ int psrc_assemble_text_prompts(const float* prefix, const float* suffix, int suf
  * every sequence with fp16_round(prompt[j]) (or the raw value if round_fp16 == 0). */
 int psrc_insert_prompt(float* x, const float* prompt, int n_seq, int L, int start,
                        int n_ctx, int D, int round_fp16, psrc_stream_t stream);
-/* backward of the replacement: grad[j,:] (+)= sum_seq dx[seq,start+j,:]; then the
- * rows are zeroed when zero_rows != 0 (no gradient reaches the layer below there). */
-int psrc_prompt_grad(float* dx, float* grad, int n_seq, int L, int start, int n_ctx,
-                     int D, int zero_rows, int accumulate, psrc_stream_t stream);
+/* backward of the replacement: grad[j,:] (+)= sum_seq r(dx[seq,start+j,:]); then the
+ * rows are zeroed when zero_rows != 0 (no gradient reaches the layer below there),
+ * in dx and in its optional act-dtype copy dx_act (the next dgrad GEMM's A operand).
+ * round_fp16 != 0: r = fp16 round trip of every per-sequence element before the sum --
+ * autograd of the reference's `.expand(N).half()` casts the incoming gradient to fp16
+ * (model.py:238,249,414); r = identity for `ctx`, which has no `.half()`. */
+int psrc_prompt_grad(float* dx, void* dx_act, int act_dtype, float* grad, int n_seq,
+                     int L, int start, int n_ctx, int D, int zero_rows, int accumulate,
+                     int round_fp16, psrc_stream_t stream);
 
 /* ------------------------------------------------------------------ heads
  * Gather one row per sequence (vision: row 0, model.py:426; text: EOT row
@@ -162,10 +167,11 @@ int psrc_gather_ln_fwd(const float* x, const int32_t* idx, const float* gamma,
                        float* rstd, int n_seq, int L, int D, float eps,
                        psrc_stream_t stream);
 /* backward: dx (fp32 [n_seq*L, D]) is fully written: zeros everywhere except the
- * gathered rows, which receive LN'(dy). */
+ * gathered rows, which receive LN'(dy); dx_act (optional) is the same in act dtype. */
 int psrc_gather_ln_bwd(const void* dy, int dy_dtype, const float* x, const int32_t* idx,
                        const float* gamma, const float* mean, const float* rstd,
-                       float* dx, int n_seq, int L, int D, psrc_stream_t stream);
+                       float* dx, void* dx_act, int act_dtype, int n_seq, int L, int D,
+                       psrc_stream_t stream);
 /* promptsrc.py:190-191 `f / f.norm(dim=-1, keepdim=True)`; inv_norm saved. */
 int psrc_l2norm_fwd(const float* x, float* y, float* inv_norm, int rows, int D,
                     psrc_stream_t stream);
@@ -207,7 +213,11 @@ int psrc_sgd_step(float* p, const float* g, float* buf, const float* lr_dev,
                   float momentum, float dampening, float weight_decay, int nesterov,
                   int first_step, int64_t n, psrc_stream_t stream);
 
-/* utility casts (fp32 <-> bf16), fp16 round trip */
+/* y[i] += a * x[i] (fp32): joins the reduce-scattered logits part of dL/dt_hat with the local
+ * L1 part; also the GPA running average over the prompt parameters (promptsrc.py:341-347). */
+int psrc_axpy(float* y, const float* x, float a, int64_t n, psrc_stream_t stream);
+
+/* utility casts (fp32 <-> bf16) */
 int psrc_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n,
               psrc_stream_t stream);
 
