@@ -15,6 +15,11 @@ from .cabi import (ACT_NONE, ACT_QUICKGELU, ACT_QUICKGELU_GRAD, BF16, F32, GEMM_
 
 LN_EPS = 1e-5  # nn.LayerNorm default used by PromptSRC/clip/model.py:153
 
+# debugging knobs (numerics bisection on the GPU box): force a kernel family, 0 = automatic
+import os as _os
+_FORCE_ATTN = int(_os.environ.get("PSRC_ATTN_BACKEND", "0"))
+_FORCE_GEMM = int(_os.environ.get("PSRC_GEMM_BACKEND", "0"))
+
 
 def _ld(t: torch.Tensor) -> int:
     assert t.dim() == 2 and t.stride(1) == 1, "row-major 2-D tensor expected"
@@ -40,7 +45,7 @@ def gemm(a, w, out, bias=None, act=ACT_NONE, aux=None, residual=None, out2=None,
     g.out, g.ldo, g.out_dtype = ptr(out), _ld(out), dt(out)
     if out2 is not None:
         g.out2, g.ldo2, g.out2_dtype = ptr(out2), _ld(out2), dt(out2)
-    g.alpha, g.backend = float(alpha), backend
+    g.alpha, g.backend = float(alpha), (backend or _FORCE_GEMM)
     cabi.check(cabi.load().psrc_gemm(C.byref(g), cabi.stream()), "psrc_gemm")
     return out
 
@@ -70,12 +75,14 @@ def layernorm_bwd(dy, x, gamma, mean, rstd, dx_out, dx_in=None, dx_act=None):
 
 
 def attn_fwd(qkv, out, lse, n_seq, L, H, causal, backend=0):
+    backend = backend or _FORCE_ATTN
     cabi.check(cabi.load().psrc_attn_fwd(ptr(qkv), ptr(out), ptr(lse), dt(qkv), n_seq, L, H, int(causal), backend,
                                          cabi.stream()), "psrc_attn_fwd")
     return out
 
 
 def attn_bwd(qkv, out, dout, lse, dqkv, n_seq, L, H, causal, backend=0):
+    backend = backend or _FORCE_ATTN
     cabi.check(cabi.load().psrc_attn_bwd(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), dt(qkv), n_seq, L, H,
                                          int(causal), backend, cabi.stream()), "psrc_attn_bwd")
     return dqkv

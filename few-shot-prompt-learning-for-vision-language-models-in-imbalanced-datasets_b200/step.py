@@ -1,0 +1,336 @@
+"""The prompted-CLIP training step (forward, losses, prompt-only backward) over the kernels.
+
+`PromptedClipStep` is the engine behind the Dassl-facing `CustomCLIP` modules in
+`trainers.py`.  It covers the PromptSRC step (CustomCLIP.forward, trainers/promptsrc.py:183-211,
+plus the loss of forward_backward :299-324) and, with the frozen-teacher branch and the vision
+prompts switched off, the CoOp step (trainers/coop.py:351-390).
+
+Multi-GPU: one process per GPU; the image batch is data-parallel, the class prompts
+are sharded by class.  Forward: all-gather of the normalised text features.  Backward:
+reduce-scatter of dL/dt_hat (each rank holds a partial sum over its images), then an all-reduce
+of the flat prompt-gradient buffer.  Loss terms are pre-scaled by the GLOBAL batch / class count
+so the summed result equals the single-device step.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import torch
+import torch.distributed as dist
+
+from . import ops
+from .engine import ACT_DTYPES, Tower, TowerWeights, _dev
+from .synthetic import ClipArch
+
+
+@dataclass
+class StepConfig:
+    arch: ClipArch
+    n_cls: int
+    batch: int                      # LOCAL batch (per rank)
+    prec: str = "bf16"              # "bf16" fast mode | "fp32" validation mode
+    n_ctx_text: int = 4
+    n_ctx_vision: int = 0           # 0: no vision prompts (CoOp) -> no vision backward
+    depth_text: int = 1             # layers 1..depth-1 carry deep prompts (model.py:343-349)
+    depth_vision: int = 0
+    ctx_per_class: bool = False     # CoOp CSC (coop.py:222-230)
+    zero_shot_branch: bool = False  # PromptSRC frozen teacher: ZS image tower + fixed text embeddings
+    w_text: float = 25.0
+    w_image: float = 10.0
+    w_logits: float = 1.0
+    focal_alpha: list | None = None  # imbalance-aware CE (coop.py:326-346); None -> plain CE
+    focal_gamma: float = 2.0
+    truncate_text: bool = True      # run text positions 0..max(EOT) only (exact)
+    world_size: int = 1
+    rank: int = 0
+    process_group: object = field(default=None, repr=False)
+
+
+def shard_range(n: int, world: int, rank: int):
+    """Contiguous class shard of rank `rank` (first n % world ranks get one extra)."""
+    base, rem = divmod(n, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+@torch.no_grad()
+def encode_text_frozen(clip_sd: dict, tokens: torch.Tensor, device, prec: str = "fp32", chunk: int = 2048):
+    """Frozen CLIP.encode_text (clip/model.py:605-618) through the kernels: the PromptSRC teacher
+    `fixed_embeddings` (trainers/promptsrc.py:122-132).  Init-time, so it runs in fp32 mode by default.
+    tokens: int64 [N, 77].  Returns un-normalised features fp32 [N, E] on `device`."""
+    from .synthetic import arch_from_state_dict
+    a = arch_from_state_dict(clip_sd)
+    act = ACT_DTYPES[prec]
+    dev = torch.device(device)
+    tw = TowerWeights(clip_sd, "transformer.", a.transformer_layers, dev, act, False)
+    tproj_t = _dev(clip_sd["text_projection"].t(), dev, act)
+    ln_g, ln_b = _dev(clip_sd["ln_final.weight"], dev), _dev(clip_sd["ln_final.bias"], dev)
+    pos = _dev(clip_sd["positional_embedding"], dev)
+    tokens = tokens.to(torch.int64).cpu()
+    Dt, E = a.transformer_width, a.embed_dim
+    out = torch.empty(tokens.shape[0], E, device=dev)
+    for lo in range(0, tokens.shape[0], chunk):
+        tk = tokens[lo:lo + chunk]
+        n = tk.shape[0]
+        eot = tk.argmax(-1)
+        L = int(eot.max()) + 1
+        emb = _dev(clip_sd["token_embedding.weight"][tk], dev)               # model.py:606
+        tower = Tower(tw, n, L, Dt, a.transformer_heads, True, act, False, dev)
+        prefix, suffix = emb[:, :1].contiguous(), emb[:, 1:].contiguous()
+        ops.assemble_text_prompts(prefix, suffix, prefix, pos, tower.x0, n, L, 0, Dt)   # + positional (model.py:608)
+        tower.forward()
+        h = torch.empty(n, Dt, device=dev, dtype=act)
+        ops.gather_ln_fwd(tower.x_final, eot.to(torch.int32).to(dev), ln_g, ln_b, h, None, None, n, L, Dt)
+        ops.gemm(h, tproj_t, out[lo:lo + n])
+    return out
+
+
+class PromptedClipStep:
+    def __init__(self, cfg: StepConfig, clip_sd: dict, tokens: torch.Tensor, device, fixed_embeddings=None):
+        """clip_sd: reference-keyed CLIP state-dict (fp32).  tokens: int64 [C, 77] tokenised prompts."""
+        self.cfg, self.device = cfg, torch.device(device)
+        a = cfg.arch
+        self.act = ACT_DTYPES[cfg.prec]
+        dev = self.device
+        C, B = cfg.n_cls, cfg.batch
+        self.c0, self.c1 = shard_range(C, cfg.world_size, cfg.rank)
+        if cfg.world_size > 1:
+            assert C % cfg.world_size == 0, "class count must divide evenly across ranks (pad the class list)"
+        self.Cl = self.c1 - self.c0
+        self.B_global = B * cfg.world_size
+        self.Dv, self.Dt, self.E = a.vision_width, a.transformer_width, a.embed_dim
+        self.scale = float(math.exp(float(clip_sd["logit_scale"])))
+
+        # ---- frozen weights in kernel layout
+        need_vb = cfg.n_ctx_vision > 0
+        self.vw = TowerWeights(clip_sd, "visual.transformer.", a.vision_layers, dev, self.act, need_vb)
+        self.tw = TowerWeights(clip_sd, "transformer.", a.transformer_layers, dev, self.act, True)
+        f = lambda k: _dev(clip_sd[k], dev)  # noqa: E731
+        self.conv_w = _dev(clip_sd["visual.conv1.weight"].reshape(self.Dv, -1), dev, self.act)
+        self.cls, self.vpos = f("visual.class_embedding"), f("visual.positional_embedding")
+        self.ln_pre = (f("visual.ln_pre.weight"), f("visual.ln_pre.bias"))
+        self.ln_post = (f("visual.ln_post.weight"), f("visual.ln_post.bias"))
+        self.ln_final = (f("ln_final.weight"), f("ln_final.bias"))
+        self.vproj = _dev(clip_sd["visual.proj"], dev, self.act)            # [Dv, E]  (dgrad operand)
+        self.vproj_t = _dev(clip_sd["visual.proj"].t(), dev, self.act)      # [E, Dv]  (forward operand)
+        self.tproj = _dev(clip_sd["text_projection"], dev, self.act)        # [Dt, E]
+        self.tproj_t = _dev(clip_sd["text_projection"].t(), dev, self.act)  # [E, Dt]
+        self.tpos = f("positional_embedding")
+
+        # ---- class tokens (this rank's shard): prefix / suffix embeddings, EOT rows
+        tokens = tokens.to(torch.int64).cpu()
+        assert tokens.shape[0] == C
+        eot_all = tokens.argmax(-1)                                          # promptsrc.py:68
+        self.Lt = int(eot_all.max()) + 1 if cfg.truncate_text else a.context_length
+        emb = clip_sd["token_embedding.weight"][tokens[self.c0:self.c1]]     # promptsrc.py:121
+        self.token_prefix = _dev(emb[:, :1], dev)                           # promptsrc.py:136
+        self.token_suffix = _dev(emb[:, 1 + cfg.n_ctx_text:], dev)          # promptsrc.py:137
+        self.eot = eot_all[self.c0:self.c1].to(torch.int32).to(dev)
+
+        # ---- towers
+        P = a.n_patches
+        self.Lv = 1 + P + cfg.n_ctx_vision
+        v_prompts = {i: (1 + P, cfg.n_ctx_vision) for i in range(1, cfg.depth_vision)} if need_vb else {}
+        t_prompts = {i: (1, cfg.n_ctx_text) for i in range(1, cfg.depth_text)}
+        self.vt = Tower(self.vw, B, self.Lv, self.Dv, a.vision_heads, False, self.act, need_vb, dev, v_prompts)
+        self.tt = Tower(self.tw, self.Cl, self.Lt, self.Dt, a.transformer_heads, True, self.act, True, dev, t_prompts)
+        self.zt = Tower(self.vw, B, 1 + P, self.Dv, a.vision_heads, False, self.act, False, dev) \
+            if cfg.zero_shot_branch else None
+
+        e = lambda *s, dt=torch.float32: torch.empty(*s, device=dev, dtype=dt)  # noqa: E731
+        self.patches = e(B * P, 3 * a.vision_patch_size ** 2, dt=self.act)
+        self.pe = e(B * P, self.Dv, dt=self.act)
+        self.hv, self.ht = e(B, self.Dv, dt=self.act), e(self.Cl, self.Dt, dt=self.act)
+        self.hv_stats, self.ht_stats = (e(B), e(B)), (e(self.Cl), e(self.Cl))
+        self.f, self.f_hat, self.f_inv = e(B, self.E), e(B, self.E), e(B)
+        self.t, self.t_hat_l, self.t_inv = e(self.Cl, self.E), e(self.Cl, self.E), e(self.Cl)
+        self.t_hat = e(C, self.E) if cfg.world_size > 1 else self.t_hat_l
+        self.logits, self.d_logits = e(B, C), e(B, C)
+        self.d_fhat, self.d_that_l = e(B, self.E), e(self.Cl, self.E)
+        self.d_that_full = e(C, self.E) if cfg.world_size > 1 else None
+        self.d_that_l1 = e(self.Cl, self.E) if cfg.world_size > 1 else None
+        self.df, self.dt_ = e(B, self.E), e(self.Cl, self.E)
+        self.df_a = e(B, self.E, dt=self.act) if self.act != torch.float32 else self.df
+        self.dt_a = e(self.Cl, self.E, dt=self.act) if self.act != torch.float32 else self.dt_
+        self.dhv, self.dht = e(B, self.Dv, dt=self.act), e(self.Cl, self.Dt, dt=self.act)
+        self.losses = e(4)
+        self.loss_scratch = e(4 * B + 2 * 296)
+        self.labels = torch.zeros(B, device=dev, dtype=torch.int32)
+        self.image = e(B, 3, a.image_resolution, a.image_resolution)
+        self.focal_alpha = torch.tensor(cfg.focal_alpha, device=dev, dtype=torch.float32) \
+            if cfg.focal_alpha is not None else None
+        if need_vb:
+            self.vpt_rounded = e(cfg.n_ctx_vision, self.Dv)
+            self.vpt_scratch = e(cfg.n_ctx_vision, self.Dv, dt=self.act)
+            self.vpt_stats = (e(cfg.n_ctx_vision), e(cfg.n_ctx_vision))
+            self.vpt_gsum = e(cfg.n_ctx_vision, self.Dv)
+
+        # ---- frozen teacher (PromptSRC): ZS image features per step, fixed text embeddings once
+        if cfg.zero_shot_branch:
+            self.zhv, self.zf = e(B, self.Dv, dt=self.act), e(B, self.E)
+            self.zf_hat, self.zs_logits = e(B, self.E), e(B, C)
+            assert fixed_embeddings is not None, "PromptSRC needs the frozen-CLIP text embeddings"
+            fe = _dev(fixed_embeddings, dev)                                   # [C, E] un-normalised
+            self.fixed_hat = e(C, self.E)
+            ops.l2norm_fwd(fe, self.fixed_hat, None)                          # promptsrc.py:196-197
+            self.fixed_hat_h = self.fixed_hat.to(torch.float16).to(torch.float32)  # `.half()` at :201 (init-time)
+            self.fixed_hat_l = self.fixed_hat[self.c0:self.c1].contiguous()
+
+        # ---- trainable prompt parameters live in ONE flat fp32 buffer (+ flat grad buffer)
+        self.param_shapes = {}
+        if cfg.ctx_per_class:
+            self.param_shapes["ctx"] = (C, cfg.n_ctx_text, self.Dt)
+        else:
+            self.param_shapes["ctx"] = (cfg.n_ctx_text, self.Dt)
+        for i in range(1, cfg.depth_text):
+            self.param_shapes[f"text.{i}"] = (cfg.n_ctx_text, self.Dt)
+        if need_vb:
+            self.param_shapes["vpt"] = (cfg.n_ctx_vision, self.Dv)
+            for i in range(1, cfg.depth_vision):
+                self.param_shapes[f"vision.{i}"] = (cfg.n_ctx_vision, self.Dv)
+        n = sum(math.prod(s) for s in self.param_shapes.values())
+        self.flat_param, self.flat_grad = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+        self.params, self.grads, off = {}, {}, 0
+        for k, s in self.param_shapes.items():
+            m = math.prod(s)
+            self.params[k] = self.flat_param[off:off + m].view(*s)
+            self.grads[k] = self.flat_grad[off:off + m].view(*s)
+            off += m
+
+    # ------------------------------------------------------------------ pieces
+    def _vision_embed(self):
+        a = self.cfg.arch
+        ops.im2col_patches(self.image, self.patches, a.image_resolution, a.vision_patch_size)
+        ops.gemm(self.patches, self.conv_w, self.pe)                         # conv1 (model.py:402)
+
+    def _vision_head(self, tower, hv, stats, f_out):
+        ops.gather_ln_fwd(tower.x_final, None, *self.ln_post, hv, *stats, tower.n_seq, tower.L, self.Dv)  # :426
+        ops.gemm(hv, self.vproj_t, f_out)                                    # :428-429
+
+    def text_features(self, ctx=None):
+        """Normalised text features of this rank's class shard -> self.t_hat_l (and self.t_hat)."""
+        cfg = self.cfg
+        ctx = self.params["ctx"] if ctx is None else ctx
+        if cfg.ctx_per_class:
+            ctx = ctx[self.c0:self.c1]
+        ops.assemble_text_prompts(self.token_prefix, self.token_suffix, ctx, self.tpos, self.tt.x0, self.Cl,
+                                  self.Lt, cfg.n_ctx_text, self.Dt, ctx_per_class=cfg.ctx_per_class)
+        self.tt.forward({i: self.params[f"text.{i}"] for i in range(1, cfg.depth_text)})
+        ops.gather_ln_fwd(self.tt.x_final, self.eot, *self.ln_final, self.ht, *self.ht_stats, self.Cl, self.Lt,
+                          self.Dt)                                           # promptsrc.py:64-68
+        ops.gemm(self.ht, self.tproj_t, self.t)
+        ops.l2norm_fwd(self.t, self.t_hat_l, self.t_inv)                     # promptsrc.py:191
+        if cfg.world_size > 1:
+            dist.all_gather_into_tensor(self.t_hat, self.t_hat_l, group=cfg.process_group)
+        return self.t_hat
+
+    def image_features(self):
+        cfg = self.cfg
+        self._vision_embed()
+        vpt = self.params["vpt"] if cfg.n_ctx_vision > 0 else None
+        ops.assemble_vision_tokens(self.pe, self.cls, self.vpos, vpt, *self.ln_pre, self.vt.x0, cfg.batch,
+                                   cfg.arch.n_patches, cfg.n_ctx_vision, self.Dv)
+        self.vt.forward({i: self.params[f"vision.{i}"] for i in range(1, cfg.depth_vision)}
+                        if cfg.n_ctx_vision > 0 else None)
+        self._vision_head(self.vt, self.hv, self.hv_stats, self.f)
+        ops.l2norm_fwd(self.f, self.f_hat, self.f_inv)                       # promptsrc.py:190
+        return self.f_hat
+
+    def zero_shot_features(self):
+        """Frozen CLIP image tower on the same patch embeddings (promptsrc.py:198-200)."""
+        cfg = self.cfg
+        ops.assemble_vision_tokens(self.pe, self.cls, self.vpos, None, *self.ln_pre, self.zt.x0, cfg.batch,
+                                   cfg.arch.n_patches, 0, self.Dv)
+        self.zt.forward()
+        self._vision_head(self.zt, self.zhv, (None, None), self.zf)
+        ops.l2norm_fwd(self.zf, self.zf_hat, None)
+        return self.zf_hat
+
+    def compute_logits(self):
+        B, C, E = self.cfg.batch, self.cfg.n_cls, self.E
+        ops.gemm_f32_strided(B, C, E, self.f_hat, E, 1, self.t_hat, E, 1, self.logits, alpha=self.scale)  # :193
+        return self.logits
+
+    # ------------------------------------------------------------------ full step
+    def forward_backward(self):
+        """Inputs: self.image / self.labels (device).  Fills self.losses, self.logits and self.flat_grad
+        (all-reduced across ranks).  The optimizer step is the caller's (trainer / bench)."""
+        cfg = self.cfg
+        B, C, E = cfg.batch, cfg.n_cls, self.E
+        zs = cfg.zero_shot_branch
+        self.text_features()
+        self.image_features()
+        self.compute_logits()
+        if zs:
+            self.zero_shot_features()
+            ops.gemm_f32_strided(B, C, E, self.zf_hat, E, 1, self.fixed_hat_h, E, 1, self.zs_logits,
+                                 alpha=self.scale)                          # promptsrc.py:201
+        multi = cfg.world_size > 1
+        d_that_l1 = self.d_that_l1 if multi else self.d_that_l
+        ops.loss_fwd_bwd(self.logits, self.labels, self.d_logits, self.losses, self.loss_scratch,
+                         zs_logits=self.zs_logits if zs else None, focal_alpha=self.focal_alpha,
+                         focal_gamma=cfg.focal_gamma,
+                         t_hat=self.t_hat_l if zs else None, t_zs=self.fixed_hat_l if zs else None,
+                         d_that=d_that_l1 if zs else None,
+                         f_hat=self.f_hat if zs else None, f_zs=self.zf_hat if zs else None,
+                         d_fhat=self.d_fhat if zs else None,
+                         w_kl=cfg.w_logits, w_text=cfg.w_text, w_image=cfg.w_image,
+                         B_global=self.B_global, Ct_global=C)
+        # ---- text side: dL/dt_hat = s * dlogits^T f_hat (+ L1)
+        if multi:
+            ops.gemm_f32_strided(C, E, B, self.d_logits, 1, C, self.f_hat, 1, E, self.d_that_full, alpha=self.scale)
+            dist.reduce_scatter_tensor(self.d_that_l, self.d_that_full, group=cfg.process_group)
+            if zs:
+                ops.axpy(self.d_that_l, self.d_that_l1, 1.0)
+        else:
+            ops.gemm_f32_strided(C, E, B, self.d_logits, 1, C, self.f_hat, 1, E, self.d_that_l, alpha=self.scale,
+                                 beta=1.0 if zs else 0.0)
+        ops.l2norm_bwd(self.d_that_l, self.t_hat_l, self.t_inv, self.dt_)
+        if self.dt_a is not self.dt_:
+            ops.cast(self.dt_, self.dt_a)
+        ops.gemm(self.dt_a, self.tproj, self.dht)                            # d(ln_final row) = dt . proj^T
+        ops.gather_ln_bwd(self.dht, self.tt.x_final, self.eot, self.ln_final[0], *self.ht_stats, self.tt.dx,
+                          self.Cl, self.Lt, self.Dt, dx_act=self.tt.dxa)
+        self.tt.backward({i: self.grads[f"text.{i}"] for i in range(1, cfg.depth_text)})
+        if cfg.ctx_per_class:
+            g = self.grads["ctx"]
+            g.zero_()
+            g[self.c0:self.c1].copy_(self.tt.dx.view(self.Cl, self.Lt, self.Dt)[:, 1:1 + cfg.n_ctx_text])
+        else:
+            ops.prompt_grad(self.tt.dx, self.grads["ctx"], self.Cl, self.Lt, 1, cfg.n_ctx_text, self.Dt,
+                            zero_rows=False, round_fp16=False)               # ctx has no .half() (promptsrc.py:160)
+        # ---- vision side (only when vision prompts exist)
+        if cfg.n_ctx_vision > 0:
+            ops.gemm_f32_strided(B, E, C, self.d_logits, C, 1, self.t_hat, 1, E, self.d_fhat, alpha=self.scale,
+                                 beta=1.0 if zs else 0.0)
+            ops.l2norm_bwd(self.d_fhat, self.f_hat, self.f_inv, self.df)
+            if self.df_a is not self.df:
+                ops.cast(self.df, self.df_a)
+            ops.gemm(self.df_a, self.vproj, self.dhv)
+            ops.gather_ln_bwd(self.dhv, self.vt.x_final, None, self.ln_post[0], *self.hv_stats, self.vt.dx, B,
+                              self.Lv, self.Dv, dx_act=self.vt.dxa)
+            self.vt.backward({i: self.grads[f"vision.{i}"] for i in range(1, cfg.depth_vision)})
+            # VPT enters before ln_pre (model.py:414-420): sum the ln_pre output grads over images, then
+            # one LayerNorm backward on the n_ctx (image-independent) rounded prompt rows
+            n = cfg.n_ctx_vision
+            ops.insert_prompt(self.vpt_rounded, self.params["vpt"], 1, n, 0, n, self.Dv, round_fp16=True)
+            ops.layernorm_fwd(self.vpt_rounded, *self.ln_pre, self.vpt_scratch, *self.vpt_stats)
+            ops.prompt_grad(self.vt.dx, self.vpt_gsum, B, self.Lv, 1 + cfg.arch.n_patches, n, self.Dv,
+                            zero_rows=False, round_fp16=False)
+            ops.layernorm_bwd(self.vpt_gsum, self.vpt_rounded, self.ln_pre[0], *self.vpt_stats, self.grads["vpt"])
+        if multi:
+            dist.all_reduce(self.flat_grad, group=cfg.process_group)
+            dist.all_reduce(self.losses, group=cfg.process_group)
+        return self.losses
+
+    @torch.no_grad()
+    def inference_logits(self, recompute_text=True):
+        """Eval branch of CustomCLIP.forward (promptsrc.py:187-193, 212-213): logits [B, C]."""
+        if recompute_text:
+            self.text_features()
+        self.image_features()
+        return self.compute_logits()
+
+    def total_loss(self):
+        return self.losses.sum()

@@ -1,0 +1,121 @@
+"""End-to-end parity of the CUDA training step against the committed reference outputs
+(tests/golden/*.npz, produced by the unmodified reference -- oracle/make_golden.py).
+
+`python tests/step_checks.py` prints every metric; `tests/test_step_gpu.py` asserts them.
+Tolerances are BASELINE.json's: logits <= 2e-2 abs in bf16 / 1e-4 in fp32 mode, prompt-gradient
+cosine >= 0.999, argmax bit-exact (fp32 mode; bf16 where the reference margin allows).
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+from helpers import cos, load_golden, promptsrc_setup, ref_name  # noqa: E402
+
+CASES = {"tiny_promptsrc": ("tiny", 3), "cfg1_promptsrc": ("ViT-B/16", 9)}
+TOL = {"fp32": dict(logits=1e-4, loss=1e-5, feat=2e-5, cos=0.9999), "bf16": dict(logits=2e-2, loss=1e-2, feat=5e-3, cos=0.999)}
+
+
+def run_promptsrc_case(name: str, prec: str, sgd: bool = True) -> dict:
+    from psrc_b200 import ops
+    arch_name, depth = CASES[name]
+    fx = load_golden(name)
+    dev = "cuda"
+    from psrc_b200 import synthetic as S
+    B = fx["label"].shape[0]
+    step, sd, fixed = promptsrc_setup(arch_name, depth, fx["tokens"], dev, prec, batch=B)
+    image, label = S.synthetic_batch(B, fx["tokens"].shape[0], S.ARCHS[arch_name].image_resolution, seed=1)
+    assert np.array_equal(label.numpy().astype(np.int32), fx["label"]), "synthetic labels drifted from the fixture"
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    torch.cuda.synchronize()
+    m = {}
+    g = lambda k: torch.from_numpy(fx[k])  # noqa: E731
+    m["fixed_embeddings_rel"] = float((fixed.cpu() - g("fixed_embeddings")).norm() / g("fixed_embeddings").norm())
+    m["logits_maxabs"] = float((step.logits.cpu() - g("logits")).abs().max())
+    m["zs_logits_maxabs"] = float((step.zs_logits.cpu() - g("zs_logits")).abs().max())
+    m["text_feat_maxabs"] = float((step.t_hat.cpu() - g("text_features")).abs().max())
+    m["image_feat_maxabs"] = float((step.f_hat.cpu() - g("image_features")).abs().max())
+    m["zs_image_feat_maxabs"] = float((step.zf_hat.cpu() - g("zs_image_features")).abs().max())
+    loss = float(step.losses.sum())
+    m["loss"] = loss
+    m["loss_rel"] = abs(loss - float(fx["loss"])) / abs(float(fx["loss"]))
+    m["ce_rel"] = abs(float(step.losses[0]) - float(fx["ce"])) / abs(float(fx["ce"]))
+    ref_logits = g("logits")
+    am = step.logits.argmax(1).cpu().numpy().astype(np.int32)
+    top2 = ref_logits.topk(2, dim=1).values
+    margin = (top2[:, 0] - top2[:, 1]).numpy()
+    decided = margin > 2 * m["logits_maxabs"]
+    m["argmax_equal_all"] = bool(np.array_equal(am, fx["argmax"]))
+    m["argmax_equal_decided"] = bool(np.array_equal(am[decided], fx["argmax"][decided]))
+    m["argmax_excluded_frac"] = float(1 - decided.mean())
+    worst, worst_key = 2.0, None
+    for k in step.params:
+        c = cos(step.grads[k], fx["grad/" + ref_name(k)])
+        m[f"gradcos/{k}"] = c
+        if c < worst:
+            worst, worst_key = c, k
+    m["gradcos_worst"], m["gradcos_worst_key"] = worst, worst_key
+    gn = torch.cat([step.grads[k].flatten().cpu() for k in step.params])
+    rn = torch.cat([torch.from_numpy(fx["grad/" + ref_name(k)]).flatten() for k in step.params])
+    m["grad_rel"] = float((gn - rn).norm() / rn.norm())
+    if sgd:  # SGD lr 0.0025 / momentum 0.9 / wd 5e-4 (make_golden: promptsrc_forward_backward)
+        lr = torch.tensor([0.0025], device=dev)
+        buf = torch.zeros_like(step.flat_param)
+        before = step.flat_param.clone()
+        ops.sgd_step(step.flat_param, step.flat_grad, buf, lr, 0.9, 0.0, 5e-4, False, True)
+        torch.cuda.synchronize()
+        d_ours = step.flat_param.cpu()  # same order as step.params
+        upd_ref = torch.cat([(torch.from_numpy(fx["after/" + ref_name(k)])).flatten() for k in step.params])
+        m["param_after_maxabs"] = float((d_ours - upd_ref).abs().max())
+        m["param_update_cos"] = cos(d_ours - before.cpu(), upd_ref - before.cpu())
+    return m
+
+
+def check(m: dict, prec: str) -> list[str]:
+    t = TOL[prec]
+    bad = []
+    if m["logits_maxabs"] > t["logits"]:
+        bad.append(f"logits max|d| {m['logits_maxabs']:.3e} > {t['logits']}")
+    if m["zs_logits_maxabs"] > t["logits"]:
+        bad.append(f"zs_logits max|d| {m['zs_logits_maxabs']:.3e} > {t['logits']}")
+    for k in ("text_feat_maxabs", "image_feat_maxabs", "zs_image_feat_maxabs"):
+        if m[k] > t["feat"]:
+            bad.append(f"{k} {m[k]:.3e} > {t['feat']}")
+    if m["loss_rel"] > t["loss"]:
+        bad.append(f"loss rel {m['loss_rel']:.3e} > {t['loss']}")
+    if m["gradcos_worst"] < t["cos"]:
+        bad.append(f"grad cosine {m['gradcos_worst']:.6f} ({m['gradcos_worst_key']}) < {t['cos']}")
+    if prec == "fp32" and not m["argmax_equal_all"]:
+        bad.append("argmax differs in fp32 mode")
+    if not m["argmax_equal_decided"]:
+        bad.append("argmax differs where the reference margin exceeds twice the logit error")
+    if "param_update_cos" in m and m["param_update_cos"] < t["cos"]:
+        bad.append(f"SGD update cosine {m['param_update_cos']:.6f} < {t['cos']}")
+    if m["fixed_embeddings_rel"] > 2e-5:
+        bad.append(f"teacher text features rel {m['fixed_embeddings_rel']:.3e}")
+    return bad
+
+
+if __name__ == "__main__":
+    names = [a for a in sys.argv[1:] if a in CASES] or list(CASES)
+    precs = [a for a in sys.argv[1:] if a in TOL] or ["fp32", "bf16"]
+    rc = 0
+    for n in names:
+        for p in precs:
+            m = run_promptsrc_case(n, p)
+            bad = check(m, p)
+            print(f"===== {n} [{p}] {'PASS' if not bad else 'FAIL: ' + '; '.join(bad)}")
+            for k, v in m.items():
+                print(f"   {k:32s} {v}")
+            rc |= bool(bad)
+    sys.exit(rc)
