@@ -1,0 +1,51 @@
+"""Algorithmic FLOP accounting of the prompted-CLIP step (SURVEY.md 8d formulas).
+
+Per block forward, N sequences of length L, width D:  F = N*L*(24*D^2 + 4*L*D)
+dgrad-only backward (weights frozen):                  B = N*L*(24*D^2 + 8*L*D)
+Host-side arithmetic only -- used by bench.py and DESIGN.md, never on the compute path.
+"""
+from __future__ import annotations
+
+
+def block_fwd(n, L, D):
+    return n * L * (24 * D * D + 4 * L * D)
+
+
+def block_bwd(n, L, D):
+    return n * L * (24 * D * D + 8 * L * D)
+
+
+def step_flops(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward, text_backward=True):
+    """Executed FLOPs of one train step on one rank (B local images, C local classes, Lt text positions)."""
+    Dv, Dt, E, P = arch.vision_width, arch.transformer_width, arch.embed_dim, arch.n_patches
+    Lv = 1 + P + n_ctx_vision
+    out = {}
+    out["patch_embed"] = 2 * B * P * (3 * arch.vision_patch_size ** 2) * Dv
+    out["vision_fwd"] = arch.vision_layers * block_fwd(B, Lv, Dv)
+    out["vision_bwd"] = arch.vision_layers * block_bwd(B, Lv, Dv) if vision_backward else 0
+    out["frozen_vision_fwd"] = arch.vision_layers * block_fwd(B, 1 + P, Dv) if zero_shot else 0
+    out["text_fwd"] = arch.transformer_layers * block_fwd(C, Lt, Dt)
+    out["text_bwd"] = arch.transformer_layers * block_bwd(C, Lt, Dt) if text_backward else 0
+    heads = 2 * B * Dv * E * (2 if zero_shot else 1) + 2 * C * Dt * E
+    out["heads"] = heads * (2 if text_backward else 1)
+    out["logits"] = 2 * B * C * E * ((2 if zero_shot else 1) + 2)   # fwd (+zs) and the two gradient GEMMs
+    out["total"] = sum(out.values())
+    return out
+
+
+def gemm_shapes(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward):
+    """(M, N, K, count) of every tcgen05 GEMM launch in one step (forward + dgrad)."""
+    Dv, Dt, P = arch.vision_width, arch.transformer_width, arch.n_patches
+    shapes = []
+
+    def tower(M, D, layers, bwd):
+        shapes.extend([(M, 3 * D, D, layers), (M, D, D, layers), (M, 4 * D, D, layers), (M, D, 4 * D, layers)])
+        if bwd:
+            shapes.extend([(M, 4 * D, D, layers), (M, D, 4 * D, layers), (M, D, D, layers), (M, D, 3 * D, layers)])
+
+    shapes.append((B * P, Dv, 3 * arch.vision_patch_size ** 2, 1))
+    tower(B * (1 + P + n_ctx_vision), Dv, arch.vision_layers, vision_backward)
+    if zero_shot:
+        tower(B * (1 + P), Dv, arch.vision_layers, False)
+    tower(C * Lt, Dt, arch.transformer_layers, True)
+    return shapes

@@ -334,3 +334,61 @@ class PromptedClipStep:
 
     def total_loss(self):
         return self.losses.sum()
+
+    # ------------------------------------------------------------------ optimizer + host-facing step
+    def init_optimizer(self, lr=0.0025, momentum=0.9, weight_decay=5e-4):
+        """torch.optim.SGD as Dassl builds it (dassl/optim/optimizer.py:105-113; PromptSRC yaml:
+        lr 0.0025, momentum 0.9, wd 5e-4) over the flat prompt buffer.  lr lives in device memory so a
+        captured graph follows the scheduler (`set_lr`)."""
+        self.lr_dev = torch.tensor([lr], device=self.device, dtype=torch.float32)
+        self.mom_buf = torch.zeros_like(self.flat_param)   # zero buffer == torch's first-step `buf = g`
+        self.sgd_hp = (float(momentum), 0.0, float(weight_decay))
+        self._graph = None
+
+    def set_lr(self, lr: float):
+        self.lr_dev.fill_(float(lr))
+
+    def sgd(self):
+        m, d, wd = self.sgd_hp
+        ops.sgd_step(self.flat_param, self.flat_grad, self.mom_buf, self.lr_dev, m, d, wd, False, False)
+
+    def train_step(self):
+        """forward + losses + prompt-only backward + SGD on the resident inputs (self.image / self.labels)."""
+        self.forward_backward()
+        self.sgd()
+        return self.losses
+
+    def capture(self, warmup: int = 2):
+        """Capture train_step into a CUDA graph (shapes are static; every kernel is stateless).  Single
+        process only: with world_size > 1 the step stays eager so NCCL runs on its own stream."""
+        assert self.cfg.world_size == 1, "graph capture is used on the single-GPU path only"
+        keep = (self.flat_param.clone(), self.mom_buf.clone())
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(warmup):
+                self.train_step()
+        torch.cuda.current_stream().wait_stream(s)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.train_step()
+        self.flat_param.copy_(keep[0])
+        self.mom_buf.copy_(keep[1])
+        self._graph = g
+        return g
+
+    def run(self):
+        """One train step on the resident inputs: graph replay when captured, eager otherwise."""
+        if getattr(self, "_graph", None) is not None:
+            self._graph.replay()
+        else:
+            self.train_step()
+        return self.losses
+
+    def train_step_host(self, image_host: torch.Tensor, label_host: torch.Tensor) -> float:
+        """The call the Dassl trainer makes per batch (PromptSRC.forward_backward, promptsrc.py:285-330):
+        host batch in (pinned fp32 [B,3,R,R], int64 [B]) -> H2D -> step -> SGD -> `loss.item()` (D2H sync)."""
+        self.image.copy_(image_host, non_blocking=True)                     # parse_batch_train :384-387
+        self.labels.copy_(label_host.to(torch.int32), non_blocking=True)
+        self.run()
+        return float(self.losses.cpu().sum())                               # :330 (16-byte D2H)
