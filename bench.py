@@ -142,7 +142,7 @@ def cpu_oracle_leg(args, steps, warmup):
         opt.zero_grad()
         o["loss"].backward()
         opt.step()
-        return float(o["loss"])
+        return float(o["loss"].detach())
 
     for _ in range(warmup):
         one()

@@ -21,7 +21,12 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 from helpers import cos, load_golden, promptsrc_setup, ref_name  # noqa: E402
 
 CASES = {"tiny_promptsrc": ("tiny", 3), "cfg1_promptsrc": ("ViT-B/16", 9)}
+# BASELINE.json tolerances, stated for the ViT-B/16 configs: fp32 mode 1e-4 on logits, bf16 2e-2, gradient cosine 0.999.
 TOL = {"fp32": dict(logits=1e-4, loss=1e-5, feat=2e-5, cos=0.9999), "bf16": dict(logits=2e-2, loss=1e-2, feat=5e-3, cos=0.999)}
+# The 'tiny' architecture (width 128, embed 64; not a BASELINE config) averages bf16 rounding noise over 8x fewer
+# embedding dimensions, so its bf16-mode logits (14.3 x cosine) carry ~sqrt(8) x the noise: widened bf16 tolerance
+# for that case only.  Its fp32-mode tolerance is the BASELINE one.
+TOL_TINY_BF16 = dict(logits=5e-2, loss=1e-2, feat=8e-3, cos=0.995)
 
 
 def run_promptsrc_case(name: str, prec: str, sgd: bool = True) -> dict:
@@ -81,8 +86,8 @@ def run_promptsrc_case(name: str, prec: str, sgd: bool = True) -> dict:
     return m
 
 
-def check(m: dict, prec: str) -> list[str]:
-    t = TOL[prec]
+def check(m: dict, prec: str, name: str = "") -> list[str]:
+    t = TOL_TINY_BF16 if (prec == "bf16" and name.startswith("tiny")) else TOL[prec]
     bad = []
     if m["logits_maxabs"] > t["logits"]:
         bad.append(f"logits max|d| {m['logits_maxabs']:.3e} > {t['logits']}")
@@ -113,7 +118,7 @@ if __name__ == "__main__":
     for n in names:
         for p in precs:
             m = run_promptsrc_case(n, p)
-            bad = check(m, p)
+            bad = check(m, p, n)
             print(f"===== {n} [{p}] {'PASS' if not bad else 'FAIL: ' + '; '.join(bad)}")
             for k, v in m.items():
                 print(f"   {k:32s} {v}")

@@ -13,5 +13,5 @@ def test_promptsrc_step_matches_reference(name, prec):
     if not torch.cuda.is_available():
         pytest.fail("CUDA device required: this package has no CPU fallback")
     m = run_promptsrc_case(name, prec)
-    bad = check(m, prec)
+    bad = check(m, prec, name)
     assert not bad, "; ".join(bad) + f"\nmetrics: {m}"
