@@ -141,6 +141,8 @@ __device__ __forceinline__ void epilogue_elem(const EpiParams& p, int row, int c
 
 void fill_epi(const psrc_gemm_args& a, EpiParams& e);
 bool gemm_tc_supported(const psrc_gemm_args& a);
-int gemm_tc(const psrc_gemm_args& a, cudaStream_t stream);
+int gemm_tc1(const psrc_gemm_args& a, cudaStream_t stream);   // single-CTA kernel (gemm_tc1.cu)
+bool gemm_pair_supported(const psrc_gemm_args& a);
+int gemm_pair(const psrc_gemm_args& a, cudaStream_t stream);  // CTA-pair kernel (gemm_pair.cu)
 
 }  // namespace psrc

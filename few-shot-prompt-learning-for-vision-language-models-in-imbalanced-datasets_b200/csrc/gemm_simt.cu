@@ -153,10 +153,11 @@ extern "C" int psrc_gemm(const psrc_gemm_args* args, psrc_stream_t stream) {
   if (a.M == 0) return PSRC_OK;
   int backend = a.backend;
   if (backend == PSRC_GEMM_AUTO) backend = gemm_tc_supported(a) ? PSRC_GEMM_TCGEN05 : PSRC_GEMM_SIMT;
-  if (backend == PSRC_GEMM_TCGEN05) {
+  if (backend == PSRC_GEMM_TCGEN05 || backend == PSRC_GEMM_TCGEN05_1CTA) {
     PSRC_CHECK_ARG(gemm_tc_supported(a),
                    "psrc_gemm: tcgen05 backend needs bf16 A/W, K%%8==0, lda/ldw%%8==0, 16B-aligned pointers");
-    return gemm_tc(a, as_stream(stream));
+    if (backend == PSRC_GEMM_TCGEN05 && gemm_pair_supported(a)) return gemm_pair(a, as_stream(stream));
+    return gemm_tc1(a, as_stream(stream));
   }
   return gemm_simt(a, as_stream(stream));
 }

@@ -1,3 +1,5 @@
+// Single-CTA tcgen05 GEMM: general fallback for epilogue combinations / shapes the CTA-pair kernel
+// (gemm_pair.cu) does not cover, and the A/B reference it is measured against.
 // Dense contraction  out = act(alpha * A . W^T + bias) + residual  on the 5th-gen tensor cores.
 //
 // Persistent, warp-specialised sm_100a kernel: one CTA per SM loops over 128 x BN output
@@ -277,7 +279,7 @@ void fill_epi(const psrc_gemm_args& a, EpiParams& e) {
              ok(a.out2, a.ldo2, a.out2_dtype);
 }
 
-int gemm_tc(const psrc_gemm_args& a, cudaStream_t stream) {
+int gemm_tc1(const psrc_gemm_args& a, cudaStream_t stream) {
   EpiParams epi;
   fill_epi(a, epi);
   // 128x256 tiles when they still fill the machine at least ~2x, else 128x128

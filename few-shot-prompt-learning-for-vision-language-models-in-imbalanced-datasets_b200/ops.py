@@ -11,7 +11,7 @@ import torch
 
 from . import cabi
 from .cabi import (ACT_NONE, ACT_QUICKGELU, ACT_QUICKGELU_GRAD, BF16, F32, GEMM_AUTO, GEMM_SIMT,
-                   GEMM_TCGEN05, dt, ptr)
+                   GEMM_TCGEN05, GEMM_TCGEN05_1CTA, dt, ptr)
 
 LN_EPS = 1e-5  # nn.LayerNorm default used by PromptSRC/clip/model.py:153
 

@@ -40,7 +40,8 @@ enum {
 };
 
 enum { PSRC_ACT_NONE = 0, PSRC_ACT_QUICKGELU = 1, PSRC_ACT_QUICKGELU_GRAD = 2 };
-enum { PSRC_GEMM_AUTO = 0, PSRC_GEMM_SIMT = 1, PSRC_GEMM_TCGEN05 = 2 };
+enum { PSRC_GEMM_AUTO = 0, PSRC_GEMM_SIMT = 1, PSRC_GEMM_TCGEN05 = 2 /* CTA-pair kernel, 1-CTA fallback */,
+       PSRC_GEMM_TCGEN05_1CTA = 3 /* force the single-CTA kernel */ };
 
 const char* psrc_last_error(void);
 int psrc_version(void);
