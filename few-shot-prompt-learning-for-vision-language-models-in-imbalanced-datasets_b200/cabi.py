@@ -17,7 +17,7 @@ LIB_PATH = PKG_DIR / "lib" / "libpsrc_b200.so"
 F32, BF16 = 0, 1
 ACT_NONE, ACT_QUICKGELU, ACT_QUICKGELU_GRAD = 0, 1, 2
 GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05, GEMM_TCGEN05_1CTA = 0, 1, 2, 3
-ATTN_AUTO, ATTN_SIMT, ATTN_MMA = 0, 1, 2
+ATTN_AUTO, ATTN_SIMT, ATTN_MMA, ATTN_TCGEN05 = 0, 1, 2, 3
 
 _vp, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 

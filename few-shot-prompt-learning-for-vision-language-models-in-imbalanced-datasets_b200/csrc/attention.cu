@@ -1,5 +1,5 @@
-// C-ABI entry points of the attention core; picks the tensor-core kernels (bf16 fast mode) or the
-// CUDA-core kernels (fp32 validation mode).  See include/psrc_b200.h for the contract.
+// C-ABI entry points of the attention core; picks the tcgen05 kernels (bf16 fast mode, 32 < L <= 256), the
+// mma.sync kernels (bf16, very short or very long sequences) or the CUDA-core kernels (fp32 validation mode).  See include/psrc_b200.h for the contract.
 #include "common.cuh"
 
 namespace psrc {
@@ -10,6 +10,10 @@ int attn_bwd_simt(const void* qkv, const void* out, const void* dout, const floa
 int attn_fwd_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s);
 int attn_bwd_mma(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int n_seq,
                  int L, int H, int causal, cudaStream_t s);
+bool attn_tc_supported(int L);
+int attn_fwd_tc(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s);
+int attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int n_seq,
+                int L, int H, int causal, cudaStream_t s);
 }  // namespace psrc
 
 using namespace psrc;
@@ -23,9 +27,13 @@ extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, 
   PSRC_CHECK_ARG(dtype == PSRC_F32 || dtype == PSRC_BF16, "psrc_attn_fwd: bad dtype");
   PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_fwd: n_seq=%d exceeds the grid limit 65535", n_seq);
   if (n_seq == 0) return PSRC_OK;
-  if (backend == 0) backend = (dtype == PSRC_BF16 && al16(qkv) && al16(out)) ? 2 : 1;
-  if (backend == 2) {
+  if (backend == 0) backend = (dtype == PSRC_BF16 && al16(qkv) && al16(out)) ? (attn_tc_supported(L) ? 3 : 2) : 1;
+  if (backend == 2 || backend == 3) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out), "psrc_attn_fwd: tensor-core backend needs aligned bf16");
+    if (backend == 3) {
+      PSRC_CHECK_ARG(attn_tc_supported(L), "psrc_attn_fwd: tcgen05 backend needs 32 < L <= 256 (L=%d)", L);
+      return attn_fwd_tc(qkv, out, lse, n_seq, L, H, causal, as_stream(stream));
+    }
     return attn_fwd_mma(qkv, out, lse, n_seq, L, H, causal, as_stream(stream));
   }
   return attn_fwd_simt(qkv, out, lse, dtype, n_seq, L, H, causal, as_stream(stream));
@@ -39,9 +47,13 @@ extern "C" int psrc_attn_bwd(const void* qkv, const void* out, const void* dout,
   PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_bwd: n_seq=%d exceeds the grid limit 65535", n_seq);
   if (n_seq == 0) return PSRC_OK;
   const bool ok16 = al16(qkv) && al16(out) && al16(dout) && al16(dqkv);
-  if (backend == 0) backend = (dtype == PSRC_BF16 && ok16) ? 2 : 1;
-  if (backend == 2) {
+  if (backend == 0) backend = (dtype == PSRC_BF16 && ok16) ? (attn_tc_supported(L) ? 3 : 2) : 1;
+  if (backend == 2 || backend == 3) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16, "psrc_attn_bwd: tensor-core backend needs aligned bf16");
+    if (backend == 3) {
+      PSRC_CHECK_ARG(attn_tc_supported(L), "psrc_attn_bwd: tcgen05 backend needs 32 < L <= 256 (L=%d)", L);
+      return attn_bwd_tc(qkv, out, dout, lse, dqkv, n_seq, L, H, causal, as_stream(stream));
+    }
     return attn_bwd_mma(qkv, out, dout, lse, dqkv, n_seq, L, H, causal, as_stream(stream));
   }
   return attn_bwd_simt(qkv, out, dout, lse, dqkv, dtype, n_seq, L, H, causal, as_stream(stream));
