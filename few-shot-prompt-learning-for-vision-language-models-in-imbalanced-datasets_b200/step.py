@@ -253,19 +253,27 @@ class PromptedClipStep:
         return self.logits
 
     # ------------------------------------------------------------------ full step
+    def forward_train(self):
+        """Forward of CustomCLIP.forward in training mode (promptsrc.py:183-201; coop.py:351-365): text features,
+        image features, logits and -- PromptSRC -- the frozen-teacher features / logits.  No loss, no backward."""
+        cfg = self.cfg
+        B, C, E = cfg.batch, cfg.n_cls, self.E
+        self.text_features()
+        self.image_features()
+        self.compute_logits()
+        if cfg.zero_shot_branch:
+            self.zero_shot_features()
+            ops.gemm_f32_strided(B, C, E, self.zf_hat, E, 1, self.fixed_hat_h, E, 1, self.zs_logits,
+                                 alpha=self.scale)                          # promptsrc.py:201
+        return self.logits
+
     def forward_backward(self):
         """Inputs: self.image / self.labels (device).  Fills self.losses, self.logits and self.flat_grad
         (all-reduced across ranks).  The optimizer step is the caller's (trainer / bench)."""
         cfg = self.cfg
-        B, C, E = cfg.batch, cfg.n_cls, self.E
+        C = cfg.n_cls
         zs = cfg.zero_shot_branch
-        self.text_features()
-        self.image_features()
-        self.compute_logits()
-        if zs:
-            self.zero_shot_features()
-            ops.gemm_f32_strided(B, C, E, self.zf_hat, E, 1, self.fixed_hat_h, E, 1, self.zs_logits,
-                                 alpha=self.scale)                          # promptsrc.py:201
+        self.forward_train()
         multi = cfg.world_size > 1
         d_that_l1 = self.d_that_l1 if multi else self.d_that_l
         ops.loss_fwd_bwd(self.logits, self.labels, self.d_logits, self.losses, self.loss_scratch,
@@ -277,7 +285,21 @@ class PromptedClipStep:
                          d_fhat=self.d_fhat if zs else None,
                          w_kl=cfg.w_logits, w_text=cfg.w_text, w_image=cfg.w_image,
                          B_global=self.B_global, Ct_global=C)
-        # ---- text side: dL/dt_hat = s * dlogits^T f_hat (+ L1)
+        self.backward_from_buffers(feature_grads=zs)
+        if multi:
+            dist.all_reduce(self.losses, group=cfg.process_group)
+        return self.losses
+
+    def backward_from_buffers(self, feature_grads: bool):
+        """Prompt-only backward from d(loss)/d(logits) in self.d_logits.  feature_grads: the direct gradients
+        w.r.t. the normalised features (PromptSRC's L1 terms, or an autograd caller's) are already in
+        self.d_fhat and self.d_that_l (single GPU) / self.d_that_l1 (sharded) and are added to the logits part.
+        Fills self.flat_grad (all-reduced across ranks)."""
+        cfg = self.cfg
+        B, C, E = cfg.batch, cfg.n_cls, self.E
+        zs = feature_grads
+        multi = cfg.world_size > 1
+        # ---- text side: dL/dt_hat = s * dlogits^T f_hat (+ direct part)
         if multi:
             ops.gemm_f32_strided(C, E, B, self.d_logits, 1, C, self.f_hat, 1, E, self.d_that_full, alpha=self.scale)
             dist.reduce_scatter_tensor(self.d_that_l, self.d_that_full, group=cfg.process_group)
@@ -321,8 +343,22 @@ class PromptedClipStep:
             ops.layernorm_bwd(self.vpt_gsum, self.vpt_rounded, self.ln_pre[0], *self.vpt_stats, self.grads["vpt"])
         if multi:
             dist.all_reduce(self.flat_grad, group=cfg.process_group)
-            dist.all_reduce(self.losses, group=cfg.process_group)
-        return self.losses
+        return self.flat_grad
+
+    def backward_from(self, g_logits, g_that=None, g_fhat=None):
+        """Autograd bridge (trainers.CustomCLIP): upstream gradients of an arbitrary loss w.r.t. logits [B, C],
+        normalised text features [C, E] and normalised image features [B, E] (fp32 device tensors or None)
+        -> prompt gradients in self.flat_grad.  Single-process form (the sharded step uses the fused loss)."""
+        assert self.cfg.world_size == 1, "the autograd bridge is single-process; sharded runs use forward_backward()"
+        if g_logits is None:
+            self.d_logits.zero_()
+        else:
+            self.d_logits.copy_(g_logits)
+        direct = g_that is not None or g_fhat is not None
+        if direct:
+            self.d_that_l.zero_() if g_that is None else self.d_that_l.copy_(g_that)
+            self.d_fhat.zero_() if g_fhat is None else self.d_fhat.copy_(g_fhat)
+        return self.backward_from_buffers(feature_grads=direct)
 
     @torch.no_grad()
     def inference_logits(self, recompute_text=True):
@@ -392,3 +428,61 @@ class PromptedClipStep:
         self.labels.copy_(label_host.to(torch.int32), non_blocking=True)
         self.run()
         return float(self.losses.cpu().sum())                               # :330 (16-byte D2H)
+
+
+class VisionInference:
+    """Evaluation path with cached text features: `SimpleTrainer.test` (dassl/engine/trainer.py:
+    445-486) calls `model_inference` once per test batch and the reference re-runs the text tower over every class
+    each time (promptsrc.py:187-188).  Here the normalised text features are computed once per
+    evaluation (`refresh_text`) and each batch costs one forward of the prompted vision tower plus the [B, C]
+    cosine-logit GEMM.  Shares the frozen weights and the live prompt parameters of a `PromptedClipStep`; owns
+    only its own activation buffers (the test batch size differs from the training one)."""
+
+    def __init__(self, step: PromptedClipStep, batch: int):
+        self.step, self.batch = step, batch
+        cfg, a, dev, act = step.cfg, step.cfg.arch, step.device, step.act
+        P = a.n_patches
+        v_prompts = {i: (1 + P, cfg.n_ctx_vision) for i in range(1, cfg.depth_vision)} if cfg.n_ctx_vision > 0 else {}
+        self.vt = Tower(step.vw, batch, step.Lv, step.Dv, a.vision_heads, False, act, False, dev, v_prompts)
+        e = lambda *s, dt=torch.float32: torch.empty(*s, device=dev, dtype=dt)  # noqa: E731
+        self.image = e(batch, 3, a.image_resolution, a.image_resolution)
+        self.patches = e(batch * P, 3 * a.vision_patch_size ** 2, dt=act)
+        self.pe = e(batch * P, step.Dv, dt=act)
+        self.hv = e(batch, step.Dv, dt=act)
+        self.f, self.f_hat = e(batch, step.E), e(batch, step.E)
+        self.logits = e(batch, cfg.n_cls)
+        self.text_valid = False
+
+    @torch.no_grad()
+    def refresh_text(self):
+        self.step.text_features()
+        self.text_valid = True
+
+    @torch.no_grad()
+    def logits_for(self, image: torch.Tensor) -> torch.Tensor:
+        """image: fp32 [b, 3, R, R] on the device, any b (chunked / zero-padded to the buffer batch).
+        Returns a fresh [b, C] fp32 tensor of logits (promptsrc.py:193)."""
+        st, cfg, a = self.step, self.step.cfg, self.step.cfg.arch
+        if not self.text_valid:
+            self.refresh_text()
+        outs = []
+        for lo in range(0, image.shape[0], self.batch):
+            chunk = image[lo:lo + self.batch]
+            b = chunk.shape[0]
+            self.image[:b].copy_(chunk)
+            if b < self.batch:
+                self.image[b:].zero_()
+            ops.im2col_patches(self.image, self.patches, a.image_resolution, a.vision_patch_size)
+            ops.gemm(self.patches, st.conv_w, self.pe)
+            vpt = st.params["vpt"] if cfg.n_ctx_vision > 0 else None
+            ops.assemble_vision_tokens(self.pe, st.cls, st.vpos, vpt, *st.ln_pre, self.vt.x0, self.batch,
+                                       a.n_patches, cfg.n_ctx_vision, st.Dv)
+            self.vt.forward({i: st.params[f"vision.{i}"] for i in range(1, cfg.depth_vision)}
+                            if cfg.n_ctx_vision > 0 else None)
+            ops.gather_ln_fwd(self.vt.x_final, None, *st.ln_post, self.hv, None, None, self.batch, self.vt.L, st.Dv)
+            ops.gemm(self.hv, st.vproj_t, self.f)
+            ops.l2norm_fwd(self.f, self.f_hat, None)
+            ops.gemm_f32_strided(self.batch, cfg.n_cls, st.E, self.f_hat, st.E, 1, st.t_hat, st.E, 1, self.logits,
+                                 alpha=st.scale)
+            outs.append(self.logits[:b].clone())
+        return outs[0] if len(outs) == 1 else torch.cat(outs, 0)

@@ -1,0 +1,665 @@
+"""Dassl-facing drop-in for the prompted-CLIP trainers.
+
+`CustomCLIP` keeps the reference module signature (`__init__(cfg, classnames, clip_model)`, `forward(image,
+label=None)`, attributes `prompt_learner / tokenized_prompts / image_encoder / text_encoder / logit_scale /
+dtype`, state-dict keys) and the trainers keep the Dassl `TrainerX` hooks (`check_cfg`, `build_model`,
+`forward_backward`, `model_inference`, `parse_batch_train`, `load_model`), registered under the reference's
+names so `train.py --trainer PromptSRC|CoOp` selects them:
+
+    PromptSRC   PromptSRC/trainers/promptsrc.py:170-213 (CustomCLIP), :216-420 (trainer)
+    CoOp        PromptSRC/trainers/coop.py:302-390 (CustomCLIP), :396-500 (trainer)
+
+All arithmetic runs in the sm_100a kernels through `step.PromptedClipStep`; there is no PyTorch fallback.
+The trainable prompt tensors are the reference's own `nn.Parameter`s (same names), re-pointed at views of the
+step's flat fp32 parameter / gradient buffers, so `state_dict()`, `load_state_dict()`, Dassl checkpoints and
+torch LR schedulers work unchanged while the optimizer update is ONE fused kernel (`FlatSGD`).
+
+When Dassl is importable (the reference checkout on `sys.path`), `TrainerX`, `TRAINER_REGISTRY`,
+`build_lr_scheduler` are Dassl's own; otherwise (GPU box: the reference does not travel) a minimal stand-in with
+the same method names is used so the same trainer code runs in tests and the benchmark.
+"""
+from __future__ import annotations
+
+import math
+import os.path as osp
+from collections import OrderedDict
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import synthetic as S
+from .step import PromptedClipStep, StepConfig, VisionInference, encode_text_frozen
+
+# ------------------------------------------------------------------ Dassl (real or stand-in)
+try:  # pragma: no cover - depends on the reference checkout being importable
+    from dassl.engine import TRAINER_REGISTRY, TrainerX
+    from dassl.optim import build_lr_scheduler as _dassl_build_sched
+    HAVE_DASSL = True
+except Exception:  # noqa: BLE001 - any import problem means "no Dassl here"
+    HAVE_DASSL = False
+    _dassl_build_sched = None
+
+    class _Registry:
+        """dassl/utils/registry.py:36-57 -- class name is the key; duplicates raise unless force=True."""
+
+        def __init__(self):
+            self._map = {}
+
+        def register(self, obj=None, force=False):
+            def deco(cls):
+                if cls.__name__ in self._map and not force:
+                    raise KeyError(f"{cls.__name__} already registered")
+                self._map[cls.__name__] = cls
+                return cls
+            return deco(obj) if obj is not None else deco
+
+        def get(self, name):
+            return self._map[name]
+
+        def registered_names(self):
+            return list(self._map)
+
+    TRAINER_REGISTRY = _Registry()
+
+    class TrainerX:
+        """The subset of dassl/engine/trainer.py (TrainerBase :74-293, SimpleTrainer :296-486, TrainerX :596-639)
+        the prompt trainers touch.  `dm` only needs `.dataset.classnames`."""
+
+        def __init__(self, cfg, dm=None, device=None):
+            self._models, self._optims, self._scheds = OrderedDict(), OrderedDict(), OrderedDict()
+            self.check_cfg(cfg)
+            self.device = torch.device(device if device is not None else "cuda")
+            self.start_epoch = self.epoch = 0
+            self.max_epoch = cfg.OPTIM.MAX_EPOCH
+            self.cfg, self.dm = cfg, dm
+            self.batch_idx, self.num_batches = 0, 1
+            self.build_model()
+
+        def check_cfg(self, cfg):
+            pass
+
+        def register_model(self, name="model", model=None, optim=None, sched=None):
+            assert name not in self._models, "Found duplicate model names"
+            self._models[name], self._optims[name], self._scheds[name] = model, optim, sched
+
+        def get_model_names(self, names=None):
+            return list(self._models) if names is None else list(names)
+
+        def set_model_mode(self, mode="train", names=None):
+            for n in self.get_model_names(names):
+                self._models[n].train() if mode == "train" else self._models[n].eval()
+
+        def update_lr(self, names=None):
+            for n in self.get_model_names(names):
+                if self._scheds[n] is not None:
+                    self._scheds[n].step()
+
+        def get_current_lr(self, names=None):
+            return self._optims[self.get_model_names(names)[0]].param_groups[0]["lr"]
+
+        def model_inference(self, input):
+            return self.model(input)
+
+        def parse_batch_train(self, batch):
+            return batch["img"].to(self.device), batch["label"].to(self.device)
+
+        def save_model(self, epoch, directory, is_best=False, val_result=None, model_name=""):
+            import os
+            for n in self.get_model_names():
+                os.makedirs(osp.join(directory, n), exist_ok=True)
+                torch.save({"state_dict": self._models[n].state_dict(), "epoch": epoch + 1,
+                            "optimizer": self._optims[n].state_dict() if self._optims[n] else None,
+                            "scheduler": self._scheds[n].state_dict() if self._scheds[n] else None,
+                            "val_result": val_result},
+                           osp.join(directory, n, model_name or f"model.pth.tar-{epoch + 1}"))
+
+
+def _get(node, path, default=None):
+    """cfg.A.B.C with a default (the reference reads keys its own extend_cfg never defines)."""
+    for k in path.split("."):
+        if node is None:
+            return default
+        node = node.get(k, None) if hasattr(node, "get") else getattr(node, k, None)
+    return default if node is None else node
+
+
+# ------------------------------------------------------------------ module tree from a flat state-dict
+class ParamTree(nn.Module):
+    """nn.Module tree whose parameter / buffer names are the dotted keys of `tensors` -- a stand-in for the
+    reference `clip.model.CLIP` (model.py:488-561) when only its state-dict is available (tests, bench)."""
+
+    def __init__(self, tensors: dict, trainable=()):
+        super().__init__()
+        for key, t in tensors.items():
+            node, parts = self, key.split(".")
+            for p in parts[:-1]:
+                if p not in node._modules:
+                    node.add_module(p, ParamTree({}))
+                node = node._modules[p]
+            t = t.detach().clone().float()
+            node.register_parameter(parts[-1], nn.Parameter(t, requires_grad=key in trainable))
+
+    def __getitem__(self, i):  # resblocks[i]
+        return self._modules[str(i)]
+
+
+def synthetic_clip(arch, seed=0, n_ctx_vision=0, n_ctx_text=0, depth_vision=0, depth_text=1, prompt_seed=100):
+    """Random-init CLIP with the reference's parameter names, including the IVLP design's VPT tensors
+    (model.py:215-217, :388-390) when depths > 0."""
+    arch = S.ARCHS[arch] if isinstance(arch, str) else arch
+    sd = S.make_clip_state_dict(arch, seed=seed)
+    deep = S.make_deep_prompts(arch, n_ctx_vision, n_ctx_text, depth_vision, depth_text, seed=prompt_seed)
+    m = ParamTree({**sd, **deep}, trainable=set(deep))
+    m.dtype = torch.float32
+    m.visual.input_resolution = arch.image_resolution
+    return m
+
+
+# ------------------------------------------------------------------ optimizer / scheduler
+class FlatSGD(torch.optim.Optimizer):
+    """torch.optim.SGD semantics (dassl/optim/optimizer.py:105-113: momentum 0.9, wd 5e-4, dampening 0, no
+    nesterov) as ONE fused kernel over the step's flat parameter buffer.  It is a torch Optimizer so Dassl's
+    LR schedulers, `update_lr` and checkpointing (`state_dict`) drive it unchanged."""
+
+    def __init__(self, step: PromptedClipStep, named_params, lr, momentum=0.9, weight_decay=5e-4, dampening=0.0,
+                 nesterov=False):
+        self._step = step
+        self._named = list(named_params)                       # [(step key, nn.Parameter)]
+        super().__init__([p for _, p in self._named], dict(lr=lr, momentum=momentum, weight_decay=weight_decay,
+                                                           dampening=dampening, nesterov=nesterov))
+        step.init_optimizer(lr=lr, momentum=momentum, weight_decay=weight_decay)
+        step.sgd_hp = (float(momentum), float(dampening), float(weight_decay))
+        self._nesterov = bool(nesterov)
+        self._lr_host = float(lr)
+        off = 0
+        for k, p in self._named:                               # momentum buffers: views, like torch's state
+            n = p.numel()
+            self.state[p]["momentum_buffer"] = step.mom_buf[off:off + n].view_as(p)
+            off += n
+
+    def sync_lr(self):
+        lr = float(self.param_groups[0]["lr"])
+        if lr != self._lr_host:
+            self._step.set_lr(lr)
+            self._lr_host = lr
+
+    def sync_grads(self):
+        """After an autograd backward, `p.grad` may be a fresh tensor (zero_grad(set_to_none)); bring it into
+        the flat gradient buffer the fused kernel reads."""
+        for k, p in self._named:
+            g = self._step.grads[k]
+            if p.grad is None:
+                g.zero_()
+            elif p.grad.data_ptr() != g.data_ptr():
+                g.copy_(p.grad)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        self.sync_lr()
+        self.sync_grads()
+        st = self._step
+        m, d, wd = st.sgd_hp
+        from . import ops
+        ops.sgd_step(st.flat_param, st.flat_grad, st.mom_buf, st.lr_dev, m, d, wd, self._nesterov, False)
+
+    def load_state_dict(self, state_dict):
+        bufs = [s.get("momentum_buffer") for s in state_dict.get("state", {}).values()]
+        groups = state_dict["param_groups"]
+        for g, sg in zip(self.param_groups, groups):
+            for k in ("lr", "momentum", "weight_decay", "dampening", "nesterov", "initial_lr"):
+                if k in sg:
+                    g[k] = sg[k]
+        for (k, p), b in zip(self._named, bufs):
+            if b is not None:
+                self.state[p]["momentum_buffer"].copy_(b)
+        self._lr_host = None
+        self.sync_lr()
+
+
+class ConstantWarmupCosine(torch.optim.lr_scheduler.LRScheduler):
+    """Stand-in for Dassl's ConstantWarmupScheduler over CosineAnnealingLR (dassl/optim/lr_scheduler.py:35-54,
+    :128-141; PromptSRC yaml: WARMUP_EPOCH 1, WARMUP_CONS_LR 1e-5), stepped once per epoch by `update_lr`."""
+
+    def __init__(self, optimizer, max_epoch, warmup_epoch=1, cons_lr=1e-5):
+        self.max_epoch, self.warmup_epoch, self.cons_lr = max_epoch, warmup_epoch, cons_lr
+        super().__init__(optimizer)
+
+    def get_lr(self):
+        e = self.last_epoch
+        if e < self.warmup_epoch:
+            return [self.cons_lr for _ in self.base_lrs]
+        # WARMUP_RECOUNT (default True, lr_scheduler.py:131-132): the cosine successor starts counting when the
+        # warm-up ends, so epoch `warmup_epoch` runs at the base lr
+        e -= self.warmup_epoch
+        return [0.5 * b * (1 + math.cos(math.pi * e / self.max_epoch)) for b in self.base_lrs]
+
+
+def build_scheduler(optim, optim_cfg):
+    if _dassl_build_sched is not None:
+        try:
+            return _dassl_build_sched(optim, optim_cfg)
+        except TypeError:
+            # Dassl's warm-up schedulers pass `verbose` positionally (lr_scheduler.py:22), which torch >= 2.7
+            # rejects: fall through to the restatement below (same lr sequence, verified on torch 1.9 semantics)
+            pass
+    warm = _get(optim_cfg, "WARMUP_EPOCH", 0) or 0
+    if _get(optim_cfg, "LR_SCHEDULER", "cosine") != "cosine":
+        raise NotImplementedError("without Dassl only the cosine scheduler of the prompt-learning yamls is provided")
+    return ConstantWarmupCosine(optim, optim_cfg.MAX_EPOCH, warm, _get(optim_cfg, "WARMUP_CONS_LR", 1e-5))
+
+
+# ------------------------------------------------------------------ tokenisation (reference tokenizer, host side)
+def _reference_tokenize(texts):
+    """`clip.tokenize` of the reference (clip/clip.py:185-221) -- integer work stays the reference's own code
+    (SURVEY a-18).  Needs PromptSRC/ on sys.path; tests and the benchmark pass `tokenized_prompts` instead."""
+    try:
+        from clip import clip as _clip
+    except Exception as e:  # noqa: BLE001
+        raise RuntimeError("CustomCLIP needs the reference tokenizer (PromptSRC/clip on sys.path) or explicit "
+                           "`tokenized_prompts=`") from e
+    return torch.cat([_clip.tokenize(t) for t in texts])
+
+
+class _TextEncoder(nn.Module):
+    """TextEncoder(clip_model) (promptsrc.py:49-57): same attribute / state-dict names, arithmetic in the kernels."""
+
+    def __init__(self, clip_model):
+        super().__init__()
+        self.transformer = clip_model.transformer
+        self.positional_embedding = clip_model.positional_embedding
+        self.ln_final = clip_model.ln_final
+        self.text_projection = clip_model.text_projection
+        self.dtype = clip_model.dtype
+
+
+class _PromptLearner(nn.Module):
+    """VLPromptLearner (promptsrc.py:72-168) / PromptLearner (coop.py:208-296): `ctx` + the frozen token
+    embeddings either side of it.  `forward()` returns the assembled prompts like the reference (a plain
+    torch.cat -- only used by external callers; the training step assembles them inside a kernel)."""
+
+    def __init__(self, ctx, token_prefix, token_suffix, tokenized_prompts, name_lens=None):
+        super().__init__()
+        self.ctx = nn.Parameter(ctx)
+        self.register_buffer("token_prefix", token_prefix)
+        self.register_buffer("token_suffix", token_suffix)
+        self.tokenized_prompts = tokenized_prompts
+        self.n_cls, self.n_ctx = token_prefix.shape[0], ctx.shape[-2]
+        self.name_lens = name_lens
+
+    def forward(self):
+        ctx = self.ctx
+        if ctx.dim() == 2:
+            ctx = ctx.unsqueeze(0).expand(self.n_cls, -1, -1)
+        return torch.cat([self.token_prefix, ctx, self.token_suffix], dim=1)
+
+
+class _Bridge(torch.autograd.Function):
+    """Autograd view of the kernel step: (prompt parameters) -> (logits, t_hat, f_hat).  backward() runs the
+    prompt-only backward kernels from the upstream gradients, whatever loss the caller composed."""
+
+    @staticmethod
+    def forward(ctx, model, image, *params):
+        st = model._step
+        st.image.copy_(image)
+        st.forward_train()
+        ctx.model = model
+        return st.logits.clone(), st.t_hat.clone(), st.f_hat.clone()
+
+    @staticmethod
+    def backward(ctx, g_logits, g_that, g_fhat):
+        st = ctx.model._step
+        st.backward_from(g_logits, g_that, g_fhat)
+        return (None, None) + tuple(st.grads[k].clone() for k, _ in ctx.model._named_prompts)
+
+
+class _CustomCLIPBase(nn.Module):
+    """Shared machinery of the CustomCLIP variants: builds the kernel step from a reference-keyed CLIP module,
+    binds the prompt nn.Parameters to the flat buffers, provides the fused / bridged / eval paths."""
+
+    def _build(self, cfg, clip_model, tokens, step_kwargs, ctx_init, fixed_embeddings=None, device=None):
+        dev = torch.device(device if device is not None else "cuda")
+        from . import ops as _ops
+        if dev.type != "cuda" and not getattr(_ops, "_FAKE_KERNELS", False):   # fakes: CPU host-logic tests only
+            raise RuntimeError("psrc_b200.CustomCLIP runs on a CUDA device only (there is no CPU path)")
+        sd = {k: v.detach().float().cpu() for k, v in clip_model.state_dict().items()}
+        arch = S.arch_from_state_dict(sd)
+        prec_cfg = step_kwargs.pop("prec_cfg", "fp16")
+        prec = "fp32" if prec_cfg == "fp32" else "bf16"      # "fp16"/"amp" -> 16-bit tensor-core mode
+        world, rank, pg = 1, 0, None
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            world, rank, pg = dist.get_world_size(), dist.get_rank(), dist.group.WORLD
+        scfg = StepConfig(arch=arch, n_cls=tokens.shape[0], batch=int(cfg.DATALOADER.TRAIN_X.BATCH_SIZE) // world,
+                          prec=prec, world_size=world, rank=rank, process_group=pg, **step_kwargs)
+        self._step = PromptedClipStep(scfg, sd, tokens, dev, fixed_embeddings=fixed_embeddings)
+        self._infer = None
+        self._test_batch = int(_get(cfg, "DATALOADER.TEST.BATCH_SIZE", 100))
+        self._use_graph = bool(_get(cfg, "TRAINER.B200.CUDA_GRAPH", True)) and world == 1
+        self._eager_steps = 0
+        emb = sd["token_embedding.weight"][tokens]
+        n_ctx = scfg.n_ctx_text
+        self.prompt_learner = _PromptLearner(ctx_init.float(), emb[:, :1].clone(), emb[:, 1 + n_ctx:].clone(), tokens)
+        self.tokenized_prompts = tokens
+        self.image_encoder = clip_model.visual
+        self.text_encoder = _TextEncoder(clip_model)
+        self.logit_scale = clip_model.logit_scale
+        self.dtype = clip_model.dtype
+        self.n_cls = tokens.shape[0]
+        self.to(dev)
+        # ---- bind the reference-named prompt parameters to the flat buffers
+        st = self._step
+        named = [("ctx", self.prompt_learner.ctx)]
+        for i in range(1, scfg.depth_text):
+            named.append((f"text.{i}", self.text_encoder.transformer.resblocks[i].VPT_shallow))
+        if scfg.n_ctx_vision > 0:
+            named.append(("vpt", self.image_encoder.VPT))
+            for i in range(1, scfg.depth_vision):
+                named.append((f"vision.{i}", self.image_encoder.transformer.resblocks[i].VPT_shallow))
+        assert [k for k, _ in named] == list(st.params), (list(st.params), [k for k, _ in named])
+        with torch.no_grad():
+            for k, p in named:
+                st.params[k].copy_(p.detach().to(dev).reshape(st.params[k].shape))
+                p.data = st.params[k]
+                p.grad = st.grads[k]
+                p.requires_grad_(True)
+        self._named_prompts = named
+        return st
+
+    # -- reference behaviour: everything except the prompts is frozen (promptsrc.py:238-247, coop.py:419-421)
+    def prompt_parameters(self):
+        return [p for _, p in self._named_prompts]
+
+    def train(self, mode: bool = True):
+        if getattr(self, "_infer", None) is not None:
+            self._infer.text_valid = False       # prompts may change between evaluations
+        return super().train(mode)
+
+    def _bridged(self, image):
+        return _Bridge.apply(self, image, *self.prompt_parameters())
+
+    def _eval_logits(self, image):
+        if self._infer is None:
+            self._infer = VisionInference(self._step, self._test_batch)
+        return self._infer.logits_for(image.float())
+
+    def make_optimizer(self, optim_cfg):
+        return FlatSGD(self._step, self._named_prompts, lr=float(optim_cfg.LR),
+                       momentum=float(_get(optim_cfg, "MOMENTUM", 0.9)),
+                       weight_decay=float(_get(optim_cfg, "WEIGHT_DECAY", 5e-4)),
+                       dampening=float(_get(optim_cfg, "SGD_DAMPNING", 0.0)),
+                       nesterov=bool(_get(optim_cfg, "SGD_NESTEROV", False)))
+
+    def train_step_fused(self, image, label, optim: FlatSGD):
+        """The trainer's fast path: H2D of the batch, ONE CUDA-graph replay of forward + fused losses +
+        prompt-only backward + SGD, and the loss terms left on the device (`.item()` is the caller's sync)."""
+        st = self._step
+        if image.shape[0] != st.cfg.batch:
+            raise RuntimeError(f"training batch {image.shape[0]} != configured per-rank batch {st.cfg.batch} "
+                               "(Dassl's train loader drops the last short batch, data_manager.py:42)")
+        optim.sync_lr()
+        st.image.copy_(image, non_blocking=True)
+        st.labels.copy_(label.to(torch.int32), non_blocking=True)
+        if self._use_graph and getattr(st, "_graph", None) is None and self._eager_steps >= 1:
+            st.capture(warmup=1)
+        self._eager_steps += 1
+        st.run()
+        if self._infer is not None:
+            self._infer.text_valid = False
+        return st.losses
+
+
+def _focal_alpha_from_cfg(cfg, n_cls):
+    """alpha_c = sum(n) / (C * n_c) from DATASET.PER_CLASS_SHOTS (coop.py:326-346, cocoop.py:219-230)."""
+    per_class = _get(cfg, "DATASET.PER_CLASS_SHOTS", None)
+    if per_class is None or len(per_class) == 0:
+        return [1.0] * n_cls
+    if isinstance(per_class, str):
+        per_class = list(map(int, per_class.strip("[]").split(",")))
+    return S.focal_alpha(list(per_class), n_cls)
+
+
+class PromptSRCCustomCLIP(_CustomCLIPBase):
+    """CustomCLIP of trainers/promptsrc.py:170-213.  Extra keyword arguments (all optional) exist because the
+    reference obtains them from the network / its tokenizer: `tokenized_prompts` int64 [C, 77],
+    `teacher_tokens` (the "a photo of a {}." prompts, promptsrc.py:124-129), `fixed_embeddings`."""
+
+    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, teacher_tokens=None,
+                 fixed_embeddings=None, device=None):
+        super().__init__()
+        T = cfg.TRAINER.PROMPTSRC
+        assert T.PROMPT_DEPTH_TEXT >= 1, "Language prompt depth should be >= 1 (promptsrc.py:77-80)"
+        n_ctx, ctx_init = int(T.N_CTX_TEXT), T.CTX_INIT
+        names = [n.replace("_", " ") for n in classnames]
+        sd_emb = clip_model.state_dict()["token_embedding.weight"].detach().float().cpu()
+        if ctx_init and n_ctx <= 4:                                          # promptsrc.py:90-98
+            ctx_init = ctx_init.replace("_", " ")
+            prefix_words = ctx_init
+        else:                                                                # :99-103
+            prefix_words = " ".join(["X"] * n_ctx)
+        if tokenized_prompts is None:
+            tokenized_prompts = _reference_tokenize([prefix_words + " " + n + "." for n in names])   # :109-111
+        tokens = torch.as_tensor(tokenized_prompts).long().cpu()
+        if ctx_init and n_ctx <= 4:
+            ctx_vectors = sd_emb[tokens[0, 1:1 + n_ctx]].clone()             # embedding of the init words
+        else:
+            ctx_vectors = torch.empty(n_ctx, sd_emb.shape[1])
+            nn.init.normal_(ctx_vectors, std=0.02)
+        dev = torch.device(device if device is not None else "cuda")
+        if fixed_embeddings is None:                                         # :116-132 frozen-CLIP teacher
+            if teacher_tokens is None:
+                same = (ctx_init or "").strip().lower() == "a photo of a"
+                teacher_tokens = tokens if same else _reference_tokenize([f"a photo of a {n}." for n in names])
+            sd = {k: v.detach().float().cpu() for k, v in clip_model.state_dict().items()}
+            fixed_embeddings = encode_text_frozen(sd, torch.as_tensor(teacher_tokens).long(), dev, prec="fp32")
+        depth_v = int(T.PROMPT_DEPTH_VISION)
+        kw = dict(prec_cfg=T.PREC, n_ctx_text=n_ctx, n_ctx_vision=int(T.N_CTX_VISION) if depth_v >= 1 else 0,
+                  depth_text=int(T.PROMPT_DEPTH_TEXT), depth_vision=depth_v, zero_shot_branch=True,
+                  w_text=float(T.TEXT_LOSS_WEIGHT), w_image=float(T.IMAGE_LOSS_WEIGHT),
+                  w_logits=float(_get(T, "LOGITS_LOSS_WEIGHT", 1.0)))      # key missing upstream
+        if _get(T, "LOSS_TYPE", "ce") == "focal":                            # promptsrc_pets_focal.py:230-247
+            kw["focal_alpha"] = _focal_alpha_from_cfg(cfg, len(classnames))
+        self._build(cfg, clip_model, tokens, kw, ctx_vectors, fixed_embeddings=fixed_embeddings, device=dev)
+        self.prompt_learner.fixed_embeddings = fixed_embeddings.to(dev)
+        self.total_epochs = cfg.OPTIM.MAX_EPOCH
+        self.cfg = cfg
+
+    def forward(self, image, label=None):
+        if not self.prompt_learner.training:
+            return self._eval_logits(image)                                  # promptsrc.py:212-213
+        st = self._step
+        logits, t_hat, f_hat = self._bridged(image.float())
+        loss_ce = F.cross_entropy(logits, label) if st.focal_alpha is None else _focal(logits, label, st)
+        return (loss_ce, t_hat, st.fixed_hat.clone(), st.zf_hat.clone(), f_hat, st.zs_logits.clone(), logits)
+
+
+def _focal(logits, label, st):
+    ce = F.cross_entropy(logits, label, reduction="none")                   # coop.py:146-163
+    pt = torch.exp(-ce)
+    return (st.focal_alpha[label] * (1 - pt) ** st.cfg.focal_gamma * ce).mean()
+
+
+class CoOpCustomCLIP(_CustomCLIPBase):
+    """CustomCLIP of trainers/coop.py:302-390 for LOSS_TYPE ce / focal, CLASS_TOKEN_POSITION 'end'."""
+
+    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None):
+        super().__init__()
+        T = cfg.TRAINER.COOP
+        self.cfg = cfg
+        self.loss_type = _get(T, "LOSS_TYPE", "ce")
+        if self.loss_type not in ("ce", "focal"):
+            raise NotImplementedError("LOSS_TYPE simclr (coop.py:316-321) is outside the accelerated path")
+        if _get(T, "CLASS_TOKEN_POSITION", "end") != "end":
+            raise NotImplementedError("CLASS_TOKEN_POSITION middle/front (coop.py:278-293) is not accelerated yet")
+        n_ctx, ctx_init, csc = int(T.N_CTX), _get(T, "CTX_INIT", ""), bool(_get(T, "CSC", False))
+        names = [n.replace("_", " ") for n in classnames]
+        sd_emb = clip_model.state_dict()["token_embedding.weight"].detach().float().cpu()
+        if ctx_init:                                                         # coop.py:218-226
+            ctx_init = ctx_init.replace("_", " ")
+            n_ctx = len(ctx_init.split(" "))
+            prefix_words = ctx_init
+        else:
+            prefix_words = " ".join(["X"] * n_ctx)
+        if tokenized_prompts is None:
+            tokenized_prompts = _reference_tokenize([prefix_words + " " + n + "." for n in names])
+        tokens = torch.as_tensor(tokenized_prompts).long().cpu()
+        if ctx_init:
+            ctx_vectors = sd_emb[tokens[0, 1:1 + n_ctx]].clone()
+        else:                                                                # :228-236
+            shape = (len(names), n_ctx, sd_emb.shape[1]) if csc else (n_ctx, sd_emb.shape[1])
+            ctx_vectors = torch.empty(*shape)
+            nn.init.normal_(ctx_vectors, std=0.02)
+        kw = dict(prec_cfg=T.PREC, n_ctx_text=n_ctx, n_ctx_vision=0, depth_text=1, depth_vision=0,
+                  ctx_per_class=csc, zero_shot_branch=False)
+        if self.loss_type == "focal":
+            kw["focal_alpha"] = _focal_alpha_from_cfg(cfg, len(classnames))
+        self._build(cfg, clip_model, tokens, kw, ctx_vectors, device=device)
+
+    def forward_once(self, image):
+        return self._bridged(image.float())[0]
+
+    def forward(self, img1, lbl=None, img2=None):
+        if not self.training:
+            return self._eval_logits(img1)
+        logits = self.forward_once(img1)
+        if lbl is None:
+            return logits
+        st = self._step
+        return F.cross_entropy(logits, lbl) if st.focal_alpha is None else _focal(logits, lbl, st)
+
+
+# ------------------------------------------------------------------ trainers
+def _load_clip(cfg, trainer_name):
+    """`load_clip_to_cpu(cfg)` of the reference trainer module (promptsrc.py:19-46, coop.py:169-190): used when the
+    trainer runs inside the reference checkout.  Tests / bench set `CLIP_MODEL_FACTORY` instead (no network)."""
+    if CLIP_MODEL_FACTORY is not None:
+        return CLIP_MODEL_FACTORY(cfg, trainer_name)
+    import importlib
+    mod = importlib.import_module(f"trainers.{trainer_name.lower()}")
+    return mod.load_clip_to_cpu(cfg)
+
+
+CLIP_MODEL_FACTORY = None   # callable(cfg, trainer_name) -> reference-keyed CLIP module (fp32)
+TOKEN_FACTORY = None        # callable(cfg, classnames) -> int64 [C, 77] tokenised prompts, or None for the reference tokenizer
+
+
+class _PromptTrainer(TrainerX):
+    MODEL_NAME = "prompt_learner"
+
+    def _tokens(self, classnames):
+        return TOKEN_FACTORY(self.cfg, classnames) if TOKEN_FACTORY is not None else None
+
+    def _finish_build(self, registered_module):
+        cfg = self.cfg
+        self.optim = self.model.make_optimizer(cfg.OPTIM)                    # SGD of optim/optimizer.py:105-113
+        self.sched = build_scheduler(self.optim, cfg.OPTIM)
+        self.register_model(self.MODEL_NAME, registered_module, self.optim, self.sched)
+
+    def model_inference(self, input):
+        return self.model(input)
+
+    def parse_batch_train(self, batch):
+        # no `.to(device)` round trip: the fused step copies the (pinned) host batch straight into its buffers
+        return batch["img"], batch["label"]
+
+    def load_model(self, directory, epoch=None):                             # promptsrc.py:390-420
+        if not directory:
+            print("Note that load_model() is skipped as no pretrained model is given")
+            return
+        model_file = "model-best.pth.tar" if epoch is None else "model.pth.tar-" + str(epoch)
+        for name in self.get_model_names():
+            path = osp.join(directory, name, model_file)
+            if not osp.exists(path):
+                raise FileNotFoundError('Model not found at "{}"'.format(path))
+            ckpt = torch.load(path, map_location="cpu", weights_only=False)
+            sd = ckpt["state_dict"]
+            for k in ("prompt_learner.token_prefix", "prompt_learner.token_suffix", "token_prefix", "token_suffix"):
+                sd.pop(k, None)                                              # ignore fixed token vectors
+            print('Loading weights to {} from "{}" (epoch = {})'.format(name, path, ckpt["epoch"]))
+            self._models[name].load_state_dict(sd, strict=False)
+
+
+@TRAINER_REGISTRY.register(force=True)
+class PromptSRC(_PromptTrainer):
+    """Drop-in for trainers/promptsrc.py:216-420."""
+    MODEL_NAME = "VLPromptLearner"
+
+    def check_cfg(self, cfg):
+        assert cfg.TRAINER.PROMPTSRC.PREC in ["fp16", "fp32", "amp"]
+
+    def build_model(self):
+        cfg = self.cfg
+        classnames = self.dm.dataset.classnames
+        clip_model = _load_clip(cfg, "PromptSRC")
+        clip_model.float()
+        self.model = PromptSRCCustomCLIP(cfg, classnames, clip_model, tokenized_prompts=self._tokens(classnames),
+                                         device=self.device)
+        self._finish_build(self.model)
+        self.total_epochs = cfg.OPTIM.MAX_EPOCH
+        self.step_counter = 1
+        # Gaussian weights of the prompt aggregation (promptsrc.py:268-273)
+        import numpy as np
+        mean, std = cfg.TRAINER.PROMPTSRC.GPA_MEAN, cfg.TRAINER.PROMPTSRC.GPA_STD
+        g = np.array([(1 / (std * np.sqrt(2 * np.pi))) * np.exp(-0.5 * ((a - mean) / std) ** 2)
+                      for a in range(1, cfg.OPTIM.MAX_EPOCH + 1)])
+        self.gauss = g / g.sum()
+        self.previous_model_gpa = None
+
+    def forward_backward(self, batch):
+        image, label = self.parse_batch_train(batch)
+        losses = self.model.train_step_fused(image, label, self.optim)
+        loss_summary = {"loss": float(losses.sum().item())}                  # promptsrc.py:330
+        last = (self.batch_idx + 1) == self.num_batches
+        if _get(self.cfg, "TRAINER.PROMPTSRC.USE_GPA", False):               # promptsrc.py:335-360
+            if last:
+                self.update_lr()
+                self.step_counter += 1
+                self._gpa_accumulate(float(self.gauss[self.step_counter - 2]))
+            if self.step_counter == self.model.total_epochs + 1:
+                print("Using GPA model for final inference...")
+                self.model._step.flat_param.copy_(self.previous_model_gpa)
+        elif last:
+            self.update_lr()
+        return loss_summary
+
+    def _gpa_accumulate(self, w):
+        """previous_model_gpa += w * state (promptsrc.py:341-347) on the trainable prompt buffer only: the frozen
+        tensors are multiplied by weights that sum to 1, i.e. unchanged."""
+        from . import ops
+        st = self.model._step
+        if self.previous_model_gpa is None:
+            self.previous_model_gpa = torch.zeros_like(st.flat_param)
+        ops.axpy(self.previous_model_gpa, st.flat_param, w)
+
+
+@TRAINER_REGISTRY.register(force=True)
+class CoOp(_PromptTrainer):
+    """Drop-in for trainers/coop.py:396-500 (LOSS_TYPE ce / focal)."""
+    MODEL_NAME = "prompt_learner"
+
+    def check_cfg(self, cfg):
+        assert cfg.TRAINER.COOP.PREC in ["fp16", "fp32", "amp"]
+
+    def build_model(self):
+        cfg = self.cfg
+        classnames = self.dm.dataset.classnames
+        clip_model = _load_clip(cfg, "CoOp")
+        clip_model.float()
+        self.model = CoOpCustomCLIP(cfg, classnames, clip_model, tokenized_prompts=self._tokens(classnames),
+                                    device=self.device)
+        self._finish_build(self.model.prompt_learner)                        # coop.py:431
+
+    def forward_backward(self, batch):
+        image, label = self.parse_batch_train(batch)
+        losses = self.model.train_step_fused(image, label, self.optim)
+        loss_summary = {"loss": float(losses.sum().item())}
+        if self.model.loss_type == "ce":                                     # coop.py:461-469: accuracy of the UPDATED prompts
+            st = self.model._step
+            with torch.no_grad():
+                st.text_features()
+                st.compute_logits()                                          # image features are prompt-independent here
+                pred = st.logits.argmax(1)
+                loss_summary["acc"] = float((pred == st.labels.long()).float().mean().item() * 100.0)
+        if (self.batch_idx + 1) == self.num_batches:
+            self.update_lr()
+        return loss_summary

@@ -68,6 +68,7 @@ class FakeKernels:
 
     def install(self, monkeypatch):
         from psrc_b200 import ops
+        monkeypatch.setattr(ops, "_FAKE_KERNELS", True, raising=False)
         for name in ("gemm", "gemm_f32_strided", "layernorm_fwd", "layernorm_bwd", "attn_fwd", "attn_bwd",
                      "im2col_patches", "assemble_vision_tokens", "assemble_text_prompts", "insert_prompt",
                      "prompt_grad", "gather_ln_fwd", "gather_ln_bwd", "l2norm_fwd", "l2norm_bwd", "loss_fwd_bwd",
@@ -202,3 +203,56 @@ class FakeKernels:
         self._rec("axpy")
         assert y.shape == x.shape
         return y
+
+
+# ---------------------------------------------------------------------------------------------
+class Cfg(dict):
+    """Attribute-access dict standing in for yacs.CfgNode in tests (the trainers only read keys)."""
+
+    def __init__(self, d=None):
+        super().__init__()
+        for k, v in (d or {}).items():
+            self[k] = Cfg(v) if isinstance(v, dict) else v
+
+    def __getattr__(self, k):
+        try:
+            return self[k]
+        except KeyError as e:
+            raise AttributeError(k) from e
+
+    def __setattr__(self, k, v):
+        self[k] = v
+
+
+def trainer_cfg(trainer="PromptSRC", batch=3, test_batch=5, max_epoch=4, depth=3, prec="fp32", **over):
+    """The keys train.py:extend_cfg + the PromptSRC/CoOp yamls define, at test sizes."""
+    c = Cfg({
+        "DATALOADER": {"TRAIN_X": {"BATCH_SIZE": batch}, "TEST": {"BATCH_SIZE": test_batch}},
+        "DATASET": {"PER_CLASS_SHOTS": []},
+        "INPUT": {"SIZE": (64, 64)},
+        "OPTIM": {"NAME": "sgd", "LR": 0.0025, "MAX_EPOCH": max_epoch, "LR_SCHEDULER": "cosine", "WARMUP_EPOCH": 1,
+                  "WARMUP_TYPE": "constant", "WARMUP_CONS_LR": 1e-5, "WARMUP_RECOUNT": True, "MOMENTUM": 0.9,
+                  "WEIGHT_DECAY": 5e-4, "SGD_DAMPNING": 0.0, "SGD_NESTEROV": False, "STEPSIZE": (-1,), "GAMMA": 0.1},
+        "TRAINER": {
+            "NAME": trainer,
+            "PROMPTSRC": {"N_CTX_VISION": 4, "N_CTX_TEXT": 4, "CTX_INIT": "a photo of a", "PREC": prec,
+                          "PROMPT_DEPTH_VISION": depth, "PROMPT_DEPTH_TEXT": depth, "TEXT_LOSS_WEIGHT": 25,
+                          "IMAGE_LOSS_WEIGHT": 10, "GPA_MEAN": 2, "GPA_STD": 1, "LOSS_TYPE": "ce"},
+            "COOP": {"N_CTX": 4, "CSC": False, "CTX_INIT": "", "PREC": prec, "CLASS_TOKEN_POSITION": "end",
+                     "LOSS_TYPE": "ce"},
+            "B200": {"CUDA_GRAPH": True},
+        },
+    })
+    for k, v in over.items():
+        node = c
+        parts = k.split(".")
+        for p in parts[:-1]:
+            node = node[p]
+        node[parts[-1]] = v
+    return c
+
+
+class FakeDM:
+    def __init__(self, classnames):
+        self.dataset = Cfg({})
+        self.dataset.classnames = list(classnames)

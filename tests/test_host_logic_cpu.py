@@ -59,3 +59,38 @@ def test_shard_range_partitions_classes():
         spans = [shard_range(n, w, r) for r in range(w)]
         assert spans[0][0] == 0 and spans[-1][1] == n
         assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+
+
+def test_trainer_dropin_builds_with_reference_names(monkeypatch):
+    """Host logic of the Dassl-facing trainer with faked kernels: registry names, model registration name,
+    reference state-dict keys, prompt parameters bound to the flat buffers, LR schedule."""
+    fk = FakeKernels()
+    fk.install(monkeypatch)
+    import trainer_checks as TC
+    from psrc_b200 import trainers as T
+    assert {"PromptSRC", "CoOp"} <= set(T.TRAINER_REGISTRY.registered_names())
+    tr, cfg, tokens = TC.make_trainer("PromptSRC", "fp32", device="cpu")
+    assert tr.get_model_names() == ["VLPromptLearner"]
+    st = tr.model._step
+    sd = tr.model.state_dict()
+    for k in ("prompt_learner.ctx", "prompt_learner.token_prefix", "prompt_learner.token_suffix", "image_encoder.VPT",
+              "image_encoder.transformer.resblocks.2.VPT_shallow", "text_encoder.transformer.resblocks.1.VPT_shallow",
+              "text_encoder.positional_embedding", "image_encoder.proj", "logit_scale"):
+        assert k in sd, k
+    trainable = {n for n, p in tr.model.named_parameters() if p.requires_grad}
+    assert len(trainable) == 6 and all(("VPT" in n) or n.endswith("ctx") for n in trainable), trainable
+    # parameters alias the flat buffer: a state-dict load lands in the buffer the kernels read
+    tr.model.load_state_dict({"prompt_learner.ctx": torch.full_like(sd["prompt_learner.ctx"], 0.5)}, strict=False)
+    assert float(st.params["ctx"].min()) == 0.5 == float(st.params["ctx"].max())
+    assert tr.model.prompt_learner.ctx.data_ptr() == st.params["ctx"].data_ptr()
+    # constant warm-up then cosine (WARMUP_RECOUNT): 1e-5, base, base * (1 + cos(pi / T)) / 2, ...
+    import math
+    lrs = []
+    for _ in range(4):
+        lrs.append(tr.optim.param_groups[0]["lr"])
+        tr.update_lr()
+    want = [1e-5, 0.0025, 0.00125 * (1 + math.cos(math.pi / 4)), 0.00125 * (1 + math.cos(2 * math.pi / 4))]
+    assert all(abs(a - b) < 1e-12 for a, b in zip(lrs, want)), (lrs, want)
+    # CoOp registers only the prompt learner (coop.py:431)
+    tr2, _, _ = TC.make_trainer("CoOp", "fp32", device="cpu")
+    assert tr2.get_model_names() == ["prompt_learner"] and list(tr2.model._step.params) == ["ctx"]

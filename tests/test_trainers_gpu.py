@@ -1,0 +1,53 @@
+"""GPU parity of the Dassl-facing drop-in (trainers.PromptSRC / CoOp, CustomCLIP) against the oracle."""
+import pytest
+import torch
+
+import trainer_checks as TC
+
+pytestmark = pytest.mark.gpu
+
+
+def _need_gpu():
+    if not torch.cuda.is_available():
+        pytest.fail("CUDA device required: this package has no CPU fallback")
+
+
+def test_promptsrc_trainer_fused_steps_match_oracle():
+    _need_gpu()
+    m = TC.check_promptsrc_trainer("fp32")
+    assert m["graph_captured"], m
+    assert max(m["loss_abs_0"], m["loss_abs_1"], m["loss_abs_2"]) < 5e-5, m
+    assert m["param_after3_maxabs"] < 1e-6 and m["update_cos"] > 0.9999, m
+    assert abs(m["lr_after_epoch"] - 0.0025) < 1e-12 and abs(m["lr_device"] - 0.0025) < 1e-9, m
+
+
+def test_customclip_forward_autograd_bridge():
+    _need_gpu()
+    m = TC.check_bridge("fp32")
+    assert m["loss_abs"] < 5e-5 and m["logits_maxabs"] < 1e-4, m
+    assert m["gradcos_worst"] > 0.9999 and m["param_after_maxabs"] < 1e-6, m
+    assert m["n_trainable"] == 2 * TC.DEPTH, m      # ctx + VPT + (depth-1) deep prompts per tower
+
+
+def test_eval_logits_cached_text_and_checkpoint_roundtrip():
+    _need_gpu()
+    m = TC.check_eval_and_checkpoint("fp32")
+    assert m["ckpt_restore_maxabs"] == 0.0 and not m["missing_state_keys"], m
+    assert m["eval_logits_maxabs"] < 1e-4 and m["eval_argmax_equal"] and m["eval_shape_ok"], m
+
+
+@pytest.mark.parametrize("loss_type", ["ce", "focal"])
+def test_coop_trainer_step(loss_type):
+    _need_gpu()
+    m = TC.check_coop("fp32", loss_type)
+    assert m["loss_abs"] < 5e-5 and m["gradcos"] > 0.9999 and m["ctx_after_maxabs"] < 1e-6, m
+    assert m["registered"] == ["prompt_learner"], m
+    if loss_type == "ce":
+        assert m["acc_abs"] < 1e-4, m
+
+
+def test_trainer_bf16_mode_runs():
+    _need_gpu()
+    m = TC.check_promptsrc_trainer("fp16")          # cfg PREC fp16 -> 16-bit tensor-core mode
+    assert max(m["loss_abs_0"], m["loss_abs_1"], m["loss_abs_2"]) < 5e-2, m
+    assert m["update_cos"] > 0.99, m
