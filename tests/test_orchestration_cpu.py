@@ -1,0 +1,120 @@
+"""CPU tests of the PRODUCT's host orchestration with the kernel layer swapped for plain-torch restatements
+(tests/torch_kernels.py): single process against the reference's golden outputs, and the class-sharded /
+data-parallel step under world_size-2 `gloo` against the single-process step."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from helpers import cos, load_golden, promptsrc_setup, ref_name
+from torch_kernels import TorchKernels
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+class _Patch:
+    """monkeypatch-like shim for subprocesses."""
+
+    def setattr(self, obj, name, value, raising=True):
+        setattr(obj, name, value)
+
+
+def test_step_orchestration_matches_reference_golden(monkeypatch):
+    """engine.py + step.py (launch order, prompt insertion / gradient routing, head + loss plumbing) driven with
+    torch math reproduce the unmodified reference's outputs for the tiny PromptSRC case."""
+    TorchKernels().install(monkeypatch)
+    fx = load_golden("tiny_promptsrc")
+    B = fx["label"].shape[0]
+    from psrc_b200 import synthetic as S
+    step, sd, fixed = promptsrc_setup("tiny", 3, fx["tokens"], "cpu", "fp32", batch=B)
+    image, label = S.synthetic_batch(B, fx["tokens"].shape[0], 64, seed=1)
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    g = lambda k: torch.from_numpy(fx[k])  # noqa: E731
+    assert float((fixed - g("fixed_embeddings")).norm() / g("fixed_embeddings").norm()) < 2e-5
+    assert float((step.logits - g("logits")).abs().max()) < 1e-4
+    assert float((step.zs_logits - g("zs_logits")).abs().max()) < 1e-4
+    assert abs(float(step.losses.sum()) - float(fx["loss"])) < 2e-5
+    assert np.array_equal(step.logits.argmax(1).numpy().astype(np.int32), fx["argmax"])
+    for k in step.params:
+        assert cos(step.grads[k], fx["grad/" + ref_name(k)]) > 0.99999, k
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _sharded_worker(rank, world, port, tokens, B_global, focal, out):
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        TorchKernels().install(_Patch())
+        from psrc_b200 import synthetic as S
+        C = tokens.shape[0]
+        alpha = S.focal_alpha(list(range(1, C + 1)), C) if focal else None
+        image, label = S.synthetic_batch(B_global, C, 64, seed=1)
+        Bl = B_global // world
+        step, sd, fixed = promptsrc_setup("tiny", 3, tokens, "cpu", "fp32", batch=Bl, world=world, rank=rank,
+                                          pg=dist.group.WORLD, focal_alpha=alpha)
+        step.image.copy_(image[rank * Bl:(rank + 1) * Bl])
+        step.labels.copy_(label[rank * Bl:(rank + 1) * Bl].int())
+        step.forward_backward()
+        step.init_optimizer()
+        step.sgd()
+        res = {"grad": step.flat_grad.clone(), "losses": step.losses.clone(), "param": step.flat_param.clone(),
+               "logits": step.logits.clone(), "t_hat": step.t_hat.clone(), "classes": (step.c0, step.c1)}
+        if rank == 0:  # single-process step on the global batch, same process (same torch math)
+            ref, _, _ = promptsrc_setup("tiny", 3, tokens, "cpu", "fp32", batch=B_global, sd=sd, fixed=fixed,
+                                        focal_alpha=alpha)
+            ref.image.copy_(image)
+            ref.labels.copy_(label.int())
+            ref.forward_backward()
+            ref.init_optimizer()
+            ref.sgd()
+            res["ref"] = {"grad": ref.flat_grad.clone(), "losses": ref.losses.clone(), "param": ref.flat_param.clone(),
+                          "logits": ref.logits.clone(), "t_hat": ref.t_hat.clone()}
+        out[rank] = res
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("focal", [False, True])
+def test_class_sharded_data_parallel_step_world2_gloo(focal):
+    """Images data-parallel, class prompts sharded by class: all-gather of t_hat, reduce-scatter of dL/dt_hat,
+    all-reduce of the flat prompt gradient and of the loss terms give the single-device step (same gradients,
+    same losses, same parameters after SGD) on every rank."""
+    from psrc_b200 import synthetic as S
+    tokens = S.synthetic_tokens(10, name_lens=[1, 2, 3, 8, 1, 1, 2, 2, 1, 2])
+    world, B_global = 2, 4
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_sharded_worker, args=(world, _free_port(), tokens, B_global, focal, out), nprocs=world, join=True)
+    ref = out[0]["ref"]
+    assert out[0]["classes"] == (0, 5) and out[1]["classes"] == (5, 10)
+    for r in range(world):
+        o = out[r]
+        assert float((o["t_hat"] - ref["t_hat"]).abs().max()) < 1e-6            # all-gathered text features
+        Bl = B_global // world
+        assert float((o["logits"] - ref["logits"][r * Bl:(r + 1) * Bl]).abs().max()) < 1e-5
+        assert float((o["losses"] - ref["losses"]).abs().max()) < 1e-5, (o["losses"], ref["losses"])
+        assert cos(o["grad"], ref["grad"]) > 0.999999
+        # per-sequence prompt gradients pass through fp16 (autograd of `.half()`, model.py:238): a different fp32
+        # summation order may flip single fp16 roundings (one ulp = 2^-14 at 0.06..0.12)
+        assert float((o["grad"] - ref["grad"]).abs().max()) < 1e-4 * float(ref["grad"].abs().max())
+        assert float((o["param"] - ref["param"]).abs().max()) < 5e-7   # lr 2.5e-3 x one fp16 ulp
+    assert float((out[0]["param"] - out[1]["param"]).abs().max()) == 0.0         # ranks stay bit-identical
