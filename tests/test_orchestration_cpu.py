@@ -116,5 +116,5 @@ def test_class_sharded_data_parallel_step_world2_gloo(focal):
         # per-sequence prompt gradients pass through fp16 (autograd of `.half()`, model.py:238): a different fp32
         # summation order may flip single fp16 roundings (one ulp = 2^-14 at 0.06..0.12)
         assert float((o["grad"] - ref["grad"]).abs().max()) < 1e-4 * float(ref["grad"].abs().max())
-        assert float((o["param"] - ref["param"]).abs().max()) < 5e-7   # lr 2.5e-3 x one fp16 ulp
+        assert float((o["param"] - ref["param"]).abs().max()) < 0.0025 * 2e-4 * float(ref["grad"].abs().max()) + 1e-7
     assert float((out[0]["param"] - out[1]["param"]).abs().max()) == 0.0         # ranks stay bit-identical
