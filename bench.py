@@ -199,6 +199,7 @@ def b200_arm(args):
     dev = torch.device("cuda", local)
     pg = None
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
         pg = dist.group.WORLD
     cabi.load()

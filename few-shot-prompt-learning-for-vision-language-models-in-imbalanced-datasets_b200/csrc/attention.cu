@@ -11,6 +11,11 @@ int attn_fwd_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H
 int attn_bwd_mma(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int n_seq,
                  int L, int H, int causal, cudaStream_t s);
 bool attn_tc_supported(int L);
+bool attn_small_supported(int L);
+int attn_fwd_small(const void* qkv, void* out, float* lse, int act_dtype, int n_seq, int L, int H, int causal,
+                   cudaStream_t s);
+int attn_bwd_small(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int act_dtype,
+                   int grad_dtype, int n_seq, int L, int H, int causal, cudaStream_t s);
 int attn_fwd_tc(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s);
 int attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int n_seq,
                 int L, int H, int causal, cudaStream_t s);
@@ -27,7 +32,14 @@ extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, 
   PSRC_CHECK_ARG(dtype == PSRC_F32 || dtype == PSRC_BF16, "psrc_attn_fwd: bad dtype");
   PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_fwd: n_seq=%d exceeds the grid limit 65535", n_seq);
   if (n_seq == 0) return PSRC_OK;
-  if (backend == 0) backend = (dtype == PSRC_BF16 && al16(qkv) && al16(out)) ? (attn_tc_supported(L) ? 3 : 2) : 1;
+  if (backend == 0)
+    backend = (dtype == PSRC_BF16 && al16(qkv) && al16(out)) ? (attn_tc_supported(L) ? 3 : (attn_small_supported(L) ? 4 : 2))
+                                                             : 1;
+  if (backend == 4) {
+    PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out) && attn_small_supported(L),
+                   "psrc_attn_fwd: short-sequence backend needs aligned bf16 and L <= 32 (L=%d)", L);
+    return attn_fwd_small(qkv, out, lse, dtype, n_seq, L, H, causal, as_stream(stream));
+  }
   if (backend == 2 || backend == 3) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out), "psrc_attn_fwd: tensor-core backend needs aligned bf16");
     if (backend == 3) {
@@ -47,7 +59,13 @@ extern "C" int psrc_attn_bwd(const void* qkv, const void* out, const void* dout,
   PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_bwd: n_seq=%d exceeds the grid limit 65535", n_seq);
   if (n_seq == 0) return PSRC_OK;
   const bool ok16 = al16(qkv) && al16(out) && al16(dout) && al16(dqkv);
-  if (backend == 0) backend = (dtype == PSRC_BF16 && ok16) ? (attn_tc_supported(L) ? 3 : 2) : 1;
+  if (backend == 0)
+    backend = (dtype == PSRC_BF16 && ok16) ? (attn_tc_supported(L) ? 3 : (attn_small_supported(L) ? 4 : 2)) : 1;
+  if (backend == 4) {
+    PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16 && attn_small_supported(L),
+                   "psrc_attn_bwd: short-sequence backend needs aligned bf16 and L <= 32 (L=%d)", L);
+    return attn_bwd_small(qkv, out, dout, lse, dqkv, dtype, dtype, n_seq, L, H, causal, as_stream(stream));
+  }
   if (backend == 2 || backend == 3) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16, "psrc_attn_bwd: tensor-core backend needs aligned bf16");
     if (backend == 3) {

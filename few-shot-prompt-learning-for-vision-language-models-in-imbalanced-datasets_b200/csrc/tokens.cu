@@ -3,9 +3,12 @@
 //   (PromptSRC/clip/model.py:401-420), text prompt assembly + positional embedding
 //   (trainers/promptsrc.py:144-168, :60; coop.py:259-296 "end"; cocoop.py:173-198),
 //   deep-prompt replacement and its gradient (model.py:232-252).
+#include <cooperative_groups.h>
 #include "common.cuh"
 
 namespace psrc {
+
+constexpr int kPgSplit = 8;   // CTAs per cluster splitting the sequences of one prompt-gradient reduction
 
 // image [B,3,R,R] fp32 -> patches [B*G*G, 3*P*P]; two elements per thread (P is even)
 template <typename T>
@@ -149,17 +152,24 @@ __global__ void insert_prompt_kernel(float* __restrict__ x, const float* __restr
 
 // grad[j, d4] (+)= sum over sequences of dx[seq, start+j, d4]; block (64, 8): x over d4, y over sequences.
 // Deterministic (fixed summation order), then optionally zeroes the rows it consumed.
-__global__ void __launch_bounds__(512)
+__global__ void __cluster_dims__(1, 1, kPgSplit) __launch_bounds__(512)
 prompt_grad_kernel(float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16, float* __restrict__ dx_f32copy,
                    float* __restrict__ grad, int n_seq, int L, int start, int n_ctx, int D, int zero_rows,
                    int accumulate, int round_fp16) {
+  // grid (D/256, n_ctx, kPgSplit): the kPgSplit CTAs of a cluster split the sequences; partial sums meet in the
+  // rank-0 CTA through distributed shared memory in a fixed order (deterministic, no atomics, no scratch)
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
   __shared__ float4 red[8][64];
+  __shared__ float4 part[64];
   const int d4 = blockIdx.x * 64 + threadIdx.x;
   const int j = blockIdx.y;
+  const int z = blockIdx.z;
   const int D4 = D / 4;
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
   if (d4 < D4) {
-    for (int seq = threadIdx.y; seq < n_seq; seq += 8) {
+#pragma unroll 4
+    for (int seq = z * 8 + threadIdx.y; seq < n_seq; seq += 8 * kPgSplit) {
       float4* p = reinterpret_cast<float4*>(dx + ((long long)seq * L + start + j) * D) + d4;
       float4 v = *p;
       if (round_fp16) v = make_float4(fp16_round(v.x), fp16_round(v.y), fp16_round(v.z), fp16_round(v.w));
@@ -174,11 +184,20 @@ prompt_grad_kernel(float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16, 
   }
   red[threadIdx.y][threadIdx.x] = s;
   __syncthreads();
-  if (threadIdx.y == 0 && d4 < D4) {
+  if (threadIdx.y == 0) {
     float4 t = red[0][threadIdx.x];
 #pragma unroll
     for (int y = 1; y < 8; ++y) {
       float4 v = red[y][threadIdx.x];
+      t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+    }
+    part[threadIdx.x] = t;
+  }
+  cluster.sync();
+  if (z == 0 && threadIdx.y == 0 && d4 < D4) {
+    float4 t = part[threadIdx.x];
+    for (int rk = 1; rk < kPgSplit; ++rk) {
+      const float4 v = cluster.map_shared_rank(part, rk)[threadIdx.x];
       t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
     }
     float4* g = reinterpret_cast<float4*>(grad + (long long)j * D) + d4;
@@ -188,6 +207,7 @@ prompt_grad_kernel(float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16, 
     }
     *g = t;
   }
+  cluster.sync();   // peers' shared memory must stay alive until rank 0 has read it
 }
 
 static int grid_for(long long n, int block) {
@@ -289,7 +309,7 @@ extern "C" int psrc_prompt_grad(float* dx, void* dx_act, int act_dtype, float* g
   PSRC_CHECK_ARG(dx && grad && D > 0 && D % 4 == 0 && start >= 0 && n_ctx >= 0 && start + n_ctx <= L && n_seq >= 0,
                  "psrc_prompt_grad: bad arguments");
   if (n_ctx == 0) return PSRC_OK;
-  dim3 grid((D / 4 + 63) / 64, n_ctx), block(64, 8);
+  dim3 grid((D / 4 + 63) / 64, n_ctx, kPgSplit), block(64, 8);
   __nv_bfloat16* a16 = (dx_act && act_dtype == PSRC_BF16) ? reinterpret_cast<__nv_bfloat16*>(dx_act) : nullptr;
   float* a32 = (dx_act && act_dtype == PSRC_F32 && dx_act != (void*)dx) ? reinterpret_cast<float*>(dx_act) : nullptr;
   prompt_grad_kernel<<<grid, block, 0, as_stream(stream)>>>(dx, a16, a32, grad, n_seq, L, start, n_ctx, D,

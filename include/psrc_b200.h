@@ -30,7 +30,7 @@ extern "C" {
 
 typedef void* psrc_stream_t; /* cudaStream_t */
 
-enum { PSRC_F32 = 0, PSRC_BF16 = 1 };
+enum { PSRC_F32 = 0, PSRC_BF16 = 1, PSRC_F16 = 2 };
 
 enum {
   PSRC_OK = 0,
@@ -107,7 +107,8 @@ int psrc_layernorm_bwd(const void* dy, int dy_dtype, const float* x,
  * softmax(q k^T / sqrt(64) [+ causal -inf mask, model.py:592-598]) v, head_dim 64.
  * qkv [n_seq*L, 3*D] with column blocks [q | k | v], head h at h*64 inside each.
  * out [n_seq*L, D]; lse fp32 [n_seq, H, L] (log-sum-exp of the scaled scores).
- * backend: 0 auto, 1 CUDA-core (any dtype), 2 mma.sync tensor-core (bf16), 3 tcgen05/TMEM (bf16, 32 < L <= 256). */
+ * backend: 0 auto, 1 CUDA-core (any dtype), 2 mma.sync tensor-core (bf16), 3 tcgen05/TMEM (bf16, 32 < L <= 256),
+ * 4 short-sequence kernel (bf16, L <= 32: the truncated text tower, one problem per half warp). */
 int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype,
                   int n_seq, int L, int H, int causal, int backend,
                   psrc_stream_t stream);
