@@ -57,6 +57,18 @@ def load_peaks():
     return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def gemm_traffic():
+    """DRAM read+write bytes per launch of the dominant GEMM flavours from the committed `ncu --set full` capture
+    (profiles/gemm_traffic.json); the mean over the captured launches, next to their algorithmic bytes."""
+    p = os.path.join(ROOT, "profiles", "gemm_traffic.json")
+    if not os.path.exists(p):
+        return None
+    rows = json.load(open(p))["per_launch"]
+    return {"dram_bytes_per_launch": sum(r["dram_read_bytes"] + r["dram_write_bytes"] for r in rows) / len(rows),
+            "algorithmic_bytes_per_launch": sum(r["algorithmic_bytes"] for r in rows) / len(rows),
+            "launches": len(rows), "source": "profiles/gemm_traffic.json (ncu --set full)"}
+
+
 # ------------------------------------------------------------------ clocks sampler
 class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -310,7 +322,7 @@ def b200_arm(args):
         ach = tot_f / (tot_ms * 1e-3) / 1e12
         roof = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05.mma + TMA + TMEM)", "achieved": round(ach, 1),
                 "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": round(ach / peaks["tf_burst"], 4),
-                "peak_source": peaks["source"] + ", burst bf16 (kernel timed alone)", "traffic": None,
+                "peak_source": peaks["source"] + ", burst bf16 (kernel timed alone)", "traffic": gemm_traffic(),
                 "launches_per_step": n_launch, "avg_launch_us": round(tot_ms / n_launch * 1e3, 2),
                 "gemm_share_of_step": round(tot_ms / ms_dev, 3), "per_shape": per_shape}
 

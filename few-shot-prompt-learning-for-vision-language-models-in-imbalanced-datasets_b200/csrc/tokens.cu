@@ -168,17 +168,31 @@ prompt_grad_kernel(float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16, 
   const int D4 = D / 4;
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
   if (d4 < D4) {
-#pragma unroll 4
-    for (int seq = z * 8 + threadIdx.y; seq < n_seq; seq += 8 * kPgSplit) {
-      float4* p = reinterpret_cast<float4*>(dx + ((long long)seq * L + start + j) * D) + d4;
-      float4 v = *p;
-      if (round_fp16) v = make_float4(fp16_round(v.x), fp16_round(v.y), fp16_round(v.z), fp16_round(v.w));
-      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-      if (zero_rows) {
-        *p = make_float4(0.f, 0.f, 0.f, 0.f);
-        const long long off = ((long long)seq * L + start + j) * D + (long long)d4 * 4;
-        if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + off) = make_uint2(0u, 0u);
-        if (dx_f32copy) *reinterpret_cast<float4*>(dx_f32copy + off) = make_float4(0.f, 0.f, 0.f, 0.f);
+    // four independent loads in flight per thread before any of the zeroing stores (which the compiler must keep
+    // ordered behind loads through the same base pointer)
+    constexpr int kU = 4;
+    const int step = 8 * kPgSplit;
+    for (int seq0 = z * 8 + threadIdx.y; seq0 < n_seq; seq0 += kU * step) {
+      float4 v[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int seq = seq0 + u * step;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (seq < n_seq) v[u] = *(reinterpret_cast<const float4*>(dx + ((long long)seq * L + start + j) * D) + d4);
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int seq = seq0 + u * step;
+        if (seq >= n_seq) break;
+        float4 w = v[u];
+        if (round_fp16) w = make_float4(fp16_round(w.x), fp16_round(w.y), fp16_round(w.z), fp16_round(w.w));
+        s.x += w.x; s.y += w.y; s.z += w.z; s.w += w.w;
+        if (zero_rows) {
+          const long long off = ((long long)seq * L + start + j) * D + (long long)d4 * 4;
+          *reinterpret_cast<float4*>(dx + off) = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + off) = make_uint2(0u, 0u);
+          if (dx_f32copy) *reinterpret_cast<float4*>(dx_f32copy + off) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
       }
     }
   }
