@@ -136,6 +136,21 @@ def make_deep_prompts(arch: ClipArch, n_ctx_vision: int, n_ctx_text: int, depth_
     return out
 
 
+def make_maple_params(arch: ClipArch, n_ctx: int, depth: int, seed: int = 200) -> dict:
+    """MaPLe's trainable coupling (trainers/maple.py:144-156): `proj` and one Linear per deeper layer
+    (nn.Linear default init scale), compound text prompts std 0.02.  Keys relative to `prompt_learner.`."""
+    g = torch.Generator().manual_seed(seed)
+    Dt, Dv = arch.transformer_width, arch.vision_width
+    bound = 1 / math.sqrt(Dt)
+    u = lambda *s: (torch.rand(*s, generator=g) * 2 - 1) * bound  # noqa: E731
+    out = {"proj.weight": u(Dv, Dt), "proj.bias": u(Dv)}
+    for i in range(depth - 1):
+        out[f"compound_prompts_text.{i}"] = torch.randn(n_ctx, Dt, generator=g) * 0.02
+        out[f"compound_prompt_projections.{i}.weight"] = u(Dv, Dt)
+        out[f"compound_prompt_projections.{i}.bias"] = u(Dv)
+    return out
+
+
 # ------------------------------------------------------------------ tokens
 def load_token_fixture(name: str = "tokens_object1000") -> np.ndarray:
     """int32 [C,77] CLIP token ids of "a photo of a object {i}." produced by the reference tokenizer

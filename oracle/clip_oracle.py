@@ -191,6 +191,26 @@ def coop_step(sd, tokens, image, label, ctx, n_ctx, vision_heads, text_heads, fo
     return {"loss": loss, "logits": logits}
 
 
+def maple_step(sd, tokens, image, label, ctx, compound_text, proj, compound_proj, n_ctx, vision_heads, text_heads,
+               focal_alpha=None, use_focal=False, truncate=None):
+    """MaPLe: MultiModalPromptLearner.forward (trainers/maple.py:190-204) + CustomCLIP.forward (:240-255).
+    ctx [n_ctx, Dt]; compound_text: list of [n_ctx, Dt] (layers 1..depth-1); proj = (W [Dv, Dt], b [Dv]) couples ctx
+    to the first-layer vision prompt (:145, :204); compound_proj: list of (W, b), one Linear per deeper layer
+    (:155-156, :199-201).  The towers replace prompts exactly like the IVLP blocks, each with `.half()`
+    (clip/model.py:287-331, :454-485; TextEncoder maple.py:62-75)."""
+    emb = sd["token_embedding.weight"][tokens]
+    prefix, suffix = emb[:, :1], emb[:, 1 + n_ctx:]                 # maple.py:168-169
+    prompts = construct_prompts(prefix, ctx, suffix)
+    shared_ctx = ctx @ proj[0].t() + proj[1]                        # :204 self.proj(self.ctx)
+    deep_v = {i + 1: t @ w.t() + b for i, (t, (w, b)) in enumerate(zip(compound_text, compound_proj))}  # :199-201
+    deep_t = {i + 1: t for i, t in enumerate(compound_text)}
+    t = text_tower(prompts, tokens.argmax(-1), sd, text_heads, deep_t, n_ctx, truncate=truncate)
+    f = vision_tower(image, sd, vision_heads, shared_ctx, deep_v)
+    logits = sd["logit_scale"].exp() * normalize(f) @ normalize(t).t()
+    loss = focal_ce(logits, label, focal_alpha) if use_focal else F.cross_entropy(logits, label)
+    return {"loss": loss, "logits": logits}
+
+
 def sgd_step(params, grads, bufs, lr, momentum=0.9, weight_decay=5e-4):
     """torch.optim.SGD as built by dassl/optim/optimizer.py:105-113 (dampening 0, no nesterov)."""
     out_p, out_b = [], []

@@ -37,6 +37,9 @@ CASES = {
     "cfg1_promptsrc": ("PromptSRC", "ViT-B/16", [f"object {i}" for i in range(100)], 4, 9, {}),
     "tiny_coop_ce": ("CoOp", "tiny", RAGGED_NAMES, 5, 0, {"TRAINER.COOP.LOSS_TYPE": "ce"}),
     "tiny_coop_focal": ("CoOp", "tiny", RAGGED_NAMES, 5, 0, {"TRAINER.COOP.LOSS_TYPE": "focal"}),
+    # MaPLe hard-codes the ViT-B widths 768 / 512 (maple.py:144-156): full-size towers, few classes
+    "vitb_maple_ce": ("MaPLe", "ViT-B/16", RAGGED_NAMES, 2, 3, {}),
+    "vitb_maple_focal": ("MaPLe", "ViT-B/16", RAGGED_NAMES, 2, 3, {"TRAINER.MAPLE.USE_FOCAL_LOSS": True}),
 }
 
 
@@ -161,6 +164,64 @@ def run_coop(name, arch_name, classnames, batch, extra):
                         **{"grad/prompt_learner.ctx": grad.numpy(), "after/prompt_learner.ctx": after.numpy()})
 
 
+def run_maple(name, arch_name, classnames, batch, depth, extra):
+    arch = S.ARCHS[arch_name]
+    sd = S.make_clip_state_dict(arch, seed=0)
+    n_ctx = 2
+    shots = S.lt_counts_cifar100(len(classnames), 50, 0.1)
+    over = {"INPUT.SIZE": (arch.image_resolution, arch.image_resolution), "TRAINER.MAPLE.N_CTX": n_ctx,
+            "TRAINER.MAPLE.PROMPT_DEPTH": depth, "TRAINER.MAPLE.CTX_INIT": "a photo of a",
+            "DATASET.PER_CLASS_SHOTS": shots}
+    over.update(extra)
+    cfg = H.make_cfg("MaPLe", **over)
+    torch.manual_seed(13)  # compound prompts and the coupling Linears are randomly initialised (maple.py:150-156)
+    tm, model = H.build_reference_model("MaPLe", cfg, classnames, sd)
+    # the two harness-side fixes without which the shipped MaPLe does not run
+    model.prompt_learner.proj.float()
+    model.image_encoder.transformer.init = model.text_encoder.transformer.init = False
+    H.freeze_like_trainer("MaPLe", model)
+    with torch.no_grad():  # seeded coupling parameters, reproducible without the reference (synthetic.make_maple_params)
+        mp_ = S.make_maple_params(arch, n_ctx, depth, seed=200)
+        named = dict(model.prompt_learner.named_parameters())
+        for k, v in mp_.items():
+            named[k].copy_(v)
+    image, label = S.synthetic_batch(batch, len(classnames), arch.image_resolution, seed=3)
+    tokens = model.tokenized_prompts.clone()
+    pl = model.prompt_learner
+    init = {n: p.detach().clone() for n, p in model.named_parameters() if p.requires_grad}
+    model.train()
+    opt = torch.optim.SGD([p for p in model.parameters() if p.requires_grad], lr=0.0035, momentum=0.9, weight_decay=5e-4)
+    loss = model(image, label)                                      # maple.py:320
+    opt.zero_grad(); loss.backward(); opt.step()                    # :321-323
+    grads = {n: p.grad.detach().clone() for n, p in model.named_parameters() if p.requires_grad}
+    after = {n: p.detach().clone() for n, p in model.named_parameters() if p.requires_grad}
+    use_focal = bool(extra.get("TRAINER.MAPLE.USE_FOCAL_LOSS", False))
+    alpha = torch.tensor(S.focal_alpha(shots, len(classnames))) if use_focal else None
+    P = {n: t.clone().requires_grad_(True) for n, t in init.items()}
+    nd = depth - 1
+    o = O.maple_step(sd, tokens, image, label, P["prompt_learner.ctx"],
+                     [P[f"prompt_learner.compound_prompts_text.{i}"] for i in range(nd)],
+                     (P["prompt_learner.proj.weight"], P["prompt_learner.proj.bias"]),
+                     [(P[f"prompt_learner.compound_prompt_projections.{i}.weight"],
+                       P[f"prompt_learner.compound_prompt_projections.{i}.bias"]) for i in range(nd)],
+                     n_ctx, arch.vision_heads, arch.transformer_heads, focal_alpha=alpha, use_focal=use_focal)
+    o["loss"].backward()
+    worst = min(cos(P[n].grad, grads[n]) for n in grads)
+    print(f"[{name}] reference loss={float(loss):.6f}; oracle |d|={abs(float(o['loss']) - float(loss)):.2e} "
+          f"worst grad cos={worst:.7f} trainable={sorted(grads)}")
+    assert abs(float(o["loss"]) - float(loss)) < 2e-5 and worst > 0.99999
+    fx = {"tokens": tokens.numpy().astype(np.int32), "label": label.numpy().astype(np.int32),
+          "loss": np.float32(float(loss)), "logits": o["logits"].detach().numpy(),
+          "shots": np.array(shots, dtype=np.int32), "n_ctx": np.int32(n_ctx), "depth": np.int32(depth)}
+    for n in grads:
+        if n.endswith(".weight"):  # [768, 512] coupling matrices: every 8th row keeps the fixture small
+            fx["grad8/" + n], fx["after8/" + n] = grads[n][::8].numpy(), after[n][::8].numpy()
+        else:
+            fx["grad/" + n], fx["after/" + n] = grads[n].numpy(), after[n].numpy()
+    fx["init/prompt_learner.ctx"] = init["prompt_learner.ctx"].numpy()
+    np.savez_compressed(os.path.join(GOLD, name + ".npz"), **fx)
+
+
 def write_token_fixtures():
     os.makedirs(S.DATA_DIR, exist_ok=True)
     toks = H.tokenize([f"a photo of a object {i}." for i in range(1000)]).numpy().astype(np.int32)
@@ -185,4 +246,6 @@ if __name__ == "__main__":
             run_promptsrc(nm, arch_name, classnames, batch, depth)
         elif trainer == "CoOp":
             run_coop(nm, arch_name, classnames, batch, extra)
+        elif trainer == "MaPLe":
+            run_maple(nm, arch_name, classnames, batch, depth, extra)
     print("golden fixtures written to", GOLD)
