@@ -72,6 +72,11 @@ SIGNATURES = {
     "psrc_sgd_step": (_i, [_vp, _vp, _vp, _vp, _f, _f, _f, _i, _i, _i64, _vp]),
     "psrc_cast": (_i, [_vp, _i, _vp, _i, _i64, _vp]),
     "psrc_axpy": (_i, [_vp, _vp, _f, _i64, _vp]),
+    "psrc_small_linear_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "psrc_small_linear_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "psrc_group_logits_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _vp]),
+    "psrc_group_logits_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _vp]),
+    "psrc_ctx_bias_grad": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
 }
 
 _lib = None

@@ -189,3 +189,58 @@ def axpy(y, x, a=1.0):
     assert y.dtype == x.dtype == torch.float32 and y.numel() == x.numel() and y.is_contiguous() and x.is_contiguous()
     cabi.check(cabi.load().psrc_axpy(ptr(y), ptr(x), float(a), y.numel(), cabi.stream()), "psrc_axpy")
     return y
+
+
+def _f32c(*ts):
+    for t in ts:
+        assert t is None or (t.dtype == torch.float32 and t.is_contiguous()), "contiguous fp32 tensor expected"
+
+
+def small_linear_fwd(x, w, b, y, relu=False):
+    """y[G,R,N] = x[G,R,K] @ w[G,N,K]^T + b[G,N] (optionally ReLU) -- see psrc_small_linear_fwd."""
+    G, R, K = x.shape
+    N = w.shape[1]
+    assert w.shape == (G, N, K) and y.shape == (G, R, N) and (b is None or b.shape == (G, N))
+    _f32c(x, w, b, y)
+    cabi.check(cabi.load().psrc_small_linear_fwd(ptr(x), ptr(w), ptr(b), ptr(y), G, R, N, K, int(relu), cabi.stream()),
+               "psrc_small_linear_fwd")
+    return y
+
+
+def small_linear_bwd(x, w, dy, dx=None, dw=None, db=None, y_relu=None, accumulate_dx=False):
+    G, R, K = x.shape
+    N = w.shape[1]
+    assert w.shape == (G, N, K) and dy.shape == (G, R, N)
+    assert dx is None or dx.shape == (G, R, K)
+    assert dw is None or (dw.shape == (G, N, K) and db is not None and db.shape == (G, N))
+    _f32c(x, w, dy, dx, dw, db, y_relu)
+    cabi.check(cabi.load().psrc_small_linear_bwd(ptr(x), ptr(w), ptr(dy), ptr(y_relu), ptr(dx), int(accumulate_dx),
+                                                 ptr(dw), ptr(db), G, R, N, K, cabi.stream()), "psrc_small_linear_bwd")
+
+
+def group_logits_fwd(f_hat, t_hat, logits, scale):
+    B, E = f_hat.shape
+    Cn = logits.shape[1]
+    assert t_hat.shape == (B * Cn, E) and logits.shape == (B, Cn)
+    _f32c(f_hat, t_hat, logits)
+    cabi.check(cabi.load().psrc_group_logits_fwd(ptr(f_hat), ptr(t_hat), ptr(logits), B, Cn, E, float(scale),
+                                                 cabi.stream()), "psrc_group_logits_fwd")
+    return logits
+
+
+def group_logits_bwd(f_hat, d_logits, d_that, scale):
+    B, E = f_hat.shape
+    Cn = d_logits.shape[1]
+    assert d_that.shape == (B * Cn, E) and d_logits.shape == (B, Cn)
+    _f32c(f_hat, d_logits, d_that)
+    cabi.check(cabi.load().psrc_group_logits_bwd(ptr(f_hat), ptr(d_logits), ptr(d_that), B, Cn, E, float(scale),
+                                                 cabi.stream()), "psrc_group_logits_bwd")
+    return d_that
+
+
+def ctx_bias_grad(gg, dctx, dbias):
+    G, n_ctx, D = gg.shape
+    assert dctx.shape == (n_ctx, D) and dbias.shape == (G, D)
+    _f32c(gg, dctx, dbias)
+    cabi.check(cabi.load().psrc_ctx_bias_grad(ptr(gg), ptr(dctx), ptr(dbias), G, n_ctx, D, cabi.stream()),
+               "psrc_ctx_bias_grad")

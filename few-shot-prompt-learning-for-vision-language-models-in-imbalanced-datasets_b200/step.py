@@ -42,6 +42,9 @@ class StepConfig:
     focal_alpha: list | None = None  # imbalance-aware CE (coop.py:326-346); None -> plain CE
     focal_gamma: float = 2.0
     truncate_text: bool = True      # run text positions 0..max(EOT) only (exact)
+    coupling: bool = False          # MaPLe: vision prompts = Linear_i(text prompts) (maple.py:145, :155-156, :199-204)
+    per_image_text: bool = False    # CoCoOp: one text-encoder pass per image, ctx + meta_net(f_hat) (cocoop.py:173-198)
+    meta_hidden: int = 0            # CoCoOp meta-net hidden width (vis_dim // 16, cocoop.py:139-143)
     world_size: int = 1
     rank: int = 0
     process_group: object = field(default=None, repr=False)
@@ -94,10 +97,19 @@ class PromptedClipStep:
         self.act = ACT_DTYPES[cfg.prec]
         dev = self.device
         C, B = cfg.n_cls, cfg.batch
-        self.c0, self.c1 = shard_range(C, cfg.world_size, cfg.rank)
-        if cfg.world_size > 1:
-            assert C % cfg.world_size == 0, "class count must divide evenly across ranks (pad the class list)"
+        self.per_image = bool(cfg.per_image_text)
+        if self.per_image:                        # CoCoOp: pure batch sharding, every rank runs all classes
+            assert cfg.n_ctx_vision == 0 and cfg.depth_text == 1 and not cfg.zero_shot_branch and not cfg.ctx_per_class
+            self.c0, self.c1 = 0, C
+        else:
+            self.c0, self.c1 = shard_range(C, cfg.world_size, cfg.rank)
+            if cfg.world_size > 1:
+                assert C % cfg.world_size == 0, "class count must divide evenly across ranks (pad the class list)"
+        if cfg.coupling:
+            assert cfg.n_ctx_vision == cfg.n_ctx_text and cfg.depth_vision == cfg.depth_text and not cfg.ctx_per_class, \
+                "MaPLe couples one vision prompt to each text prompt (maple.py:150-156)"
         self.Cl = self.c1 - self.c0
+        self.share_text = cfg.world_size > 1 and not self.per_image   # all-gather t_hat / reduce-scatter dt_hat
         self.B_global = B * cfg.world_size
         self.Dv, self.Dt, self.E = a.vision_width, a.transformer_width, a.embed_dim
         self.scale = float(math.exp(float(clip_sd["logit_scale"])))
@@ -127,6 +139,9 @@ class PromptedClipStep:
         self.token_prefix = _dev(emb[:, :1], dev)                           # promptsrc.py:136
         self.token_suffix = _dev(emb[:, 1 + cfg.n_ctx_text:], dev)          # promptsrc.py:137
         self.eot = eot_all[self.c0:self.c1].to(torch.int32).to(dev)
+        self.n_text_seq = self.Cl * (B if self.per_image else 1)
+        if self.per_image:
+            self.eot = self.eot.repeat(B).contiguous()                       # sequence s = image * C + class
 
         # ---- towers
         P = a.n_patches
@@ -134,26 +149,28 @@ class PromptedClipStep:
         v_prompts = {i: (1 + P, cfg.n_ctx_vision) for i in range(1, cfg.depth_vision)} if need_vb else {}
         t_prompts = {i: (1, cfg.n_ctx_text) for i in range(1, cfg.depth_text)}
         self.vt = Tower(self.vw, B, self.Lv, self.Dv, a.vision_heads, False, self.act, need_vb, dev, v_prompts)
-        self.tt = Tower(self.tw, self.Cl, self.Lt, self.Dt, a.transformer_heads, True, self.act, True, dev, t_prompts)
+        self.tt = Tower(self.tw, self.n_text_seq, self.Lt, self.Dt, a.transformer_heads, True, self.act, True, dev,
+                        t_prompts)
         self.zt = Tower(self.vw, B, 1 + P, self.Dv, a.vision_heads, False, self.act, False, dev) \
             if cfg.zero_shot_branch else None
 
         e = lambda *s, dt=torch.float32: torch.empty(*s, device=dev, dtype=dt)  # noqa: E731
         self.patches = e(B * P, 3 * a.vision_patch_size ** 2, dt=self.act)
         self.pe = e(B * P, self.Dv, dt=self.act)
-        self.hv, self.ht = e(B, self.Dv, dt=self.act), e(self.Cl, self.Dt, dt=self.act)
-        self.hv_stats, self.ht_stats = (e(B), e(B)), (e(self.Cl), e(self.Cl))
+        Ts = self.n_text_seq
+        self.hv, self.ht = e(B, self.Dv, dt=self.act), e(Ts, self.Dt, dt=self.act)
+        self.hv_stats, self.ht_stats = (e(B), e(B)), (e(Ts), e(Ts))
         self.f, self.f_hat, self.f_inv = e(B, self.E), e(B, self.E), e(B)
-        self.t, self.t_hat_l, self.t_inv = e(self.Cl, self.E), e(self.Cl, self.E), e(self.Cl)
-        self.t_hat = e(C, self.E) if cfg.world_size > 1 else self.t_hat_l
+        self.t, self.t_hat_l, self.t_inv = e(Ts, self.E), e(Ts, self.E), e(Ts)
+        self.t_hat = e(C, self.E) if self.share_text else self.t_hat_l
         self.logits, self.d_logits = e(B, C), e(B, C)
-        self.d_fhat, self.d_that_l = e(B, self.E), e(self.Cl, self.E)
-        self.d_that_full = e(C, self.E) if cfg.world_size > 1 else None
-        self.d_that_l1 = e(self.Cl, self.E) if cfg.world_size > 1 else None
-        self.df, self.dt_ = e(B, self.E), e(self.Cl, self.E)
+        self.d_fhat, self.d_that_l = e(B, self.E), e(Ts, self.E)
+        self.d_that_full = e(C, self.E) if self.share_text else None
+        self.d_that_l1 = e(self.Cl, self.E) if self.share_text else None
+        self.df, self.dt_ = e(B, self.E), e(Ts, self.E)
         self.df_a = e(B, self.E, dt=self.act) if self.act != torch.float32 else self.df
-        self.dt_a = e(self.Cl, self.E, dt=self.act) if self.act != torch.float32 else self.dt_
-        self.dhv, self.dht = e(B, self.Dv, dt=self.act), e(self.Cl, self.Dt, dt=self.act)
+        self.dt_a = e(Ts, self.E, dt=self.act) if self.act != torch.float32 else self.dt_
+        self.dhv, self.dht = e(B, self.Dv, dt=self.act), e(Ts, self.Dt, dt=self.act)
         self.losses = e(4)
         self.loss_scratch = e(4 * B + 2 * 296)
         self.labels = torch.zeros(B, device=dev, dtype=torch.int32)
@@ -185,18 +202,59 @@ class PromptedClipStep:
             self.param_shapes["ctx"] = (cfg.n_ctx_text, self.Dt)
         for i in range(1, cfg.depth_text):
             self.param_shapes[f"text.{i}"] = (cfg.n_ctx_text, self.Dt)
-        if need_vb:
+        nd = cfg.depth_vision
+        if cfg.coupling:
+            # MaPLe: the vision prompts are DERIVED (maple.py:199-204); trainable are the coupling Linears.
+            # Index 0 = `proj` (ctx -> first-layer prompt), i >= 1 = compound_prompt_projections[i-1].
+            for i in range(nd):
+                self.param_shapes[f"couple.w.{i}"] = (self.Dv, self.Dt)
+            for i in range(nd):
+                self.param_shapes[f"couple.b.{i}"] = (self.Dv,)
+        elif need_vb:
             self.param_shapes["vpt"] = (cfg.n_ctx_vision, self.Dv)
             for i in range(1, cfg.depth_vision):
                 self.param_shapes[f"vision.{i}"] = (cfg.n_ctx_vision, self.Dv)
+        if self.per_image:
+            Hm = cfg.meta_hidden
+            assert Hm > 0, "CoCoOp needs the meta-net hidden width"
+            self.param_shapes.update({"meta.w1": (Hm, self.E), "meta.b1": (Hm,), "meta.w2": (self.Dt, Hm),
+                                      "meta.b2": (self.Dt,)})
         n = sum(math.prod(s) for s in self.param_shapes.values())
         self.flat_param, self.flat_grad = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
-        self.params, self.grads, off = {}, {}, 0
+        self.params, self.grads, self.param_offsets, off = {}, {}, {}, 0
         for k, s in self.param_shapes.items():
             m = math.prod(s)
             self.params[k] = self.flat_param[off:off + m].view(*s)
             self.grads[k] = self.flat_grad[off:off + m].view(*s)
+            self.param_offsets[k] = off
             off += m
+        # vision prompt values / gradients by layer (0 = the shallow prompt appended before ln_pre)
+        if cfg.coupling:
+            n_c = cfg.n_ctx_text
+
+            def span(buf, first, count, *shape):
+                o = self.param_offsets[first]
+                return buf[o:o + count].view(*shape)
+            nt = nd * n_c * self.Dt              # ctx, text.1 .. text.{nd-1} are contiguous: X of the batched Linear
+            self.couple_x, self.couple_dx = (span(b_, "ctx", nt, nd, n_c, self.Dt) for b_ in (self.flat_param, self.flat_grad))
+            nw = nd * self.Dv * self.Dt
+            self.couple_w, self.couple_dw = (span(b_, "couple.w.0", nw, nd, self.Dv, self.Dt)
+                                             for b_ in (self.flat_param, self.flat_grad))
+            self.couple_b, self.couple_db = (span(b_, "couple.b.0", nd * self.Dv, nd, self.Dv)
+                                             for b_ in (self.flat_param, self.flat_grad))
+            self.vis_prompt, self.vis_prompt_grad = e(nd, n_c, self.Dv), e(nd, n_c, self.Dv)
+            self.vprompts = {i: self.vis_prompt[i] for i in range(nd)}
+            self.vgrads = {i: self.vis_prompt_grad[i] for i in range(nd)}
+        elif need_vb:
+            self.vprompts = {0: self.params["vpt"], **{i: self.params[f"vision.{i}"] for i in range(1, nd)}}
+            self.vgrads = {0: self.grads["vpt"], **{i: self.grads[f"vision.{i}"] for i in range(1, nd)}}
+        else:
+            self.vprompts, self.vgrads = {}, {}
+        if self.per_image:
+            Hm = cfg.meta_hidden
+            self.meta_h, self.meta_dh = e(1, B, Hm), e(1, B, Hm)
+            self.ctx_bias, self.d_ctx_bias = e(1, B, self.Dt), e(1, B, self.Dt)
+            self.ctx_gg = e(B, cfg.n_ctx_text, self.Dt)
 
     # ------------------------------------------------------------------ pieces
     def _vision_embed(self):
@@ -214,25 +272,40 @@ class PromptedClipStep:
         ctx = self.params["ctx"] if ctx is None else ctx
         if cfg.ctx_per_class:
             ctx = ctx[self.c0:self.c1]
-        ops.assemble_text_prompts(self.token_prefix, self.token_suffix, ctx, self.tpos, self.tt.x0, self.Cl,
-                                  self.Lt, cfg.n_ctx_text, self.Dt, ctx_per_class=cfg.ctx_per_class)
+        if self.per_image:
+            # meta-net on the normalised image features, one context shift per image (cocoop.py:139-143, :185-188)
+            p = self.params
+            ops.small_linear_fwd(self.f_hat.view(1, cfg.batch, self.E), p["meta.w1"].unsqueeze(0),
+                                 p["meta.b1"].unsqueeze(0), self.meta_h, relu=True)
+            ops.small_linear_fwd(self.meta_h, p["meta.w2"].unsqueeze(0), p["meta.b2"].unsqueeze(0), self.ctx_bias)
+            ops.assemble_text_prompts(self.token_prefix, self.token_suffix, ctx, self.tpos, self.tt.x0, self.Cl,
+                                      self.Lt, cfg.n_ctx_text, self.Dt, ctx_bias=self.ctx_bias.view(cfg.batch, self.Dt),
+                                      n_groups=cfg.batch)
+        else:
+            ops.assemble_text_prompts(self.token_prefix, self.token_suffix, ctx, self.tpos, self.tt.x0, self.Cl,
+                                      self.Lt, cfg.n_ctx_text, self.Dt, ctx_per_class=cfg.ctx_per_class)
         self.tt.forward({i: self.params[f"text.{i}"] for i in range(1, cfg.depth_text)})
-        ops.gather_ln_fwd(self.tt.x_final, self.eot, *self.ln_final, self.ht, *self.ht_stats, self.Cl, self.Lt,
-                          self.Dt)                                           # promptsrc.py:64-68
+        ops.gather_ln_fwd(self.tt.x_final, self.eot, *self.ln_final, self.ht, *self.ht_stats, self.n_text_seq,
+                          self.Lt, self.Dt)                                  # promptsrc.py:64-68
         ops.gemm(self.ht, self.tproj_t, self.t)
         ops.l2norm_fwd(self.t, self.t_hat_l, self.t_inv)                     # promptsrc.py:191
-        if cfg.world_size > 1:
+        if self.share_text:
             dist.all_gather_into_tensor(self.t_hat, self.t_hat_l, group=cfg.process_group)
         return self.t_hat
+
+    def couple_prompts(self):
+        """MaPLe: vision prompt of layer i = Linear_i(text prompt of layer i) (maple.py:199-204), one launch."""
+        if self.cfg.coupling:
+            ops.small_linear_fwd(self.couple_x, self.couple_w, self.couple_b, self.vis_prompt)
 
     def image_features(self):
         cfg = self.cfg
         self._vision_embed()
-        vpt = self.params["vpt"] if cfg.n_ctx_vision > 0 else None
+        self.couple_prompts()
+        vpt = self.vprompts[0] if cfg.n_ctx_vision > 0 else None
         ops.assemble_vision_tokens(self.pe, self.cls, self.vpos, vpt, *self.ln_pre, self.vt.x0, cfg.batch,
                                    cfg.arch.n_patches, cfg.n_ctx_vision, self.Dv)
-        self.vt.forward({i: self.params[f"vision.{i}"] for i in range(1, cfg.depth_vision)}
-                        if cfg.n_ctx_vision > 0 else None)
+        self.vt.forward(self.vprompts if cfg.n_ctx_vision > 0 else None)
         self._vision_head(self.vt, self.hv, self.hv_stats, self.f)
         ops.l2norm_fwd(self.f, self.f_hat, self.f_inv)                       # promptsrc.py:190
         return self.f_hat
@@ -249,7 +322,10 @@ class PromptedClipStep:
 
     def compute_logits(self):
         B, C, E = self.cfg.batch, self.cfg.n_cls, self.E
-        ops.gemm_f32_strided(B, C, E, self.f_hat, E, 1, self.t_hat, E, 1, self.logits, alpha=self.scale)  # :193
+        if self.per_image:
+            ops.group_logits_fwd(self.f_hat, self.t_hat_l, self.logits, self.scale)   # cocoop.py:249-252
+        else:
+            ops.gemm_f32_strided(B, C, E, self.f_hat, E, 1, self.t_hat, E, 1, self.logits, alpha=self.scale)  # :193
         return self.logits
 
     # ------------------------------------------------------------------ full step
@@ -258,8 +334,12 @@ class PromptedClipStep:
         image features, logits and -- PromptSRC -- the frozen-teacher features / logits.  No loss, no backward."""
         cfg = self.cfg
         B, C, E = cfg.batch, cfg.n_cls, self.E
-        self.text_features()
-        self.image_features()
+        if self.per_image:                 # the context shift needs the image features first (cocoop.py:241-246)
+            self.image_features()
+            self.text_features()
+        else:
+            self.text_features()
+            self.image_features()
         self.compute_logits()
         if cfg.zero_shot_branch:
             self.zero_shot_features()
@@ -275,7 +355,7 @@ class PromptedClipStep:
         zs = cfg.zero_shot_branch
         self.forward_train()
         multi = cfg.world_size > 1
-        d_that_l1 = self.d_that_l1 if multi else self.d_that_l
+        d_that_l1 = self.d_that_l1 if self.share_text else self.d_that_l
         ops.loss_fwd_bwd(self.logits, self.labels, self.d_logits, self.losses, self.loss_scratch,
                          zs_logits=self.zs_logits if zs else None, focal_alpha=self.focal_alpha,
                          focal_gamma=cfg.focal_gamma,
@@ -300,7 +380,10 @@ class PromptedClipStep:
         zs = feature_grads
         multi = cfg.world_size > 1
         # ---- text side: dL/dt_hat = s * dlogits^T f_hat (+ direct part)
-        if multi:
+        if self.per_image:
+            assert not zs
+            ops.group_logits_bwd(self.f_hat, self.d_logits, self.d_that_l, self.scale)
+        elif self.share_text:
             ops.gemm_f32_strided(C, E, B, self.d_logits, 1, C, self.f_hat, 1, E, self.d_that_full, alpha=self.scale)
             dist.reduce_scatter_tensor(self.d_that_l, self.d_that_full, group=cfg.process_group)
             if zs:
@@ -313,9 +396,22 @@ class PromptedClipStep:
             ops.cast(self.dt_, self.dt_a)
         ops.gemm(self.dt_a, self.tproj, self.dht)                            # d(ln_final row) = dt . proj^T
         ops.gather_ln_bwd(self.dht, self.tt.x_final, self.eot, self.ln_final[0], *self.ht_stats, self.tt.dx,
-                          self.Cl, self.Lt, self.Dt, dx_act=self.tt.dxa)
+                          self.n_text_seq, self.Lt, self.Dt, dx_act=self.tt.dxa)
         self.tt.backward({i: self.grads[f"text.{i}"] for i in range(1, cfg.depth_text)})
-        if cfg.ctx_per_class:
+        if self.per_image:
+            # context rows summed over the classes of each image, then split into d ctx / d bias and pushed
+            # through the meta-net (autograd of cocoop.py:185-188, :139-143); the image tower is frozen
+            n_c, rows = cfg.n_ctx_text, self.Cl * self.Lt
+            for g in range(B):
+                ops.prompt_grad(self.tt.dx[g * rows:(g + 1) * rows], self.ctx_gg[g], self.Cl, self.Lt, 1, n_c,
+                                self.Dt, zero_rows=False, round_fp16=False)
+            ops.ctx_bias_grad(self.ctx_gg, self.grads["ctx"], self.d_ctx_bias.view(B, self.Dt))
+            p, g_ = self.params, self.grads
+            ops.small_linear_bwd(self.meta_h, p["meta.w2"].unsqueeze(0), self.d_ctx_bias, dx=self.meta_dh,
+                                 dw=g_["meta.w2"].unsqueeze(0), db=g_["meta.b2"].unsqueeze(0))
+            ops.small_linear_bwd(self.f_hat.view(1, B, self.E), p["meta.w1"].unsqueeze(0), self.meta_dh,
+                                 dw=g_["meta.w1"].unsqueeze(0), db=g_["meta.b1"].unsqueeze(0), y_relu=self.meta_h)
+        elif cfg.ctx_per_class:
             g = self.grads["ctx"]
             g.zero_()
             g[self.c0:self.c1].copy_(self.tt.dx.view(self.Cl, self.Lt, self.Dt)[:, 1:1 + cfg.n_ctx_text])
@@ -332,15 +428,19 @@ class PromptedClipStep:
             ops.gemm(self.df_a, self.vproj, self.dhv)
             ops.gather_ln_bwd(self.dhv, self.vt.x_final, None, self.ln_post[0], *self.hv_stats, self.vt.dx, B,
                               self.Lv, self.Dv, dx_act=self.vt.dxa)
-            self.vt.backward({i: self.grads[f"vision.{i}"] for i in range(1, cfg.depth_vision)})
+            self.vt.backward(self.vgrads)
             # VPT enters before ln_pre (model.py:414-420): sum the ln_pre output grads over images, then
             # one LayerNorm backward on the n_ctx (image-independent) rounded prompt rows
             n = cfg.n_ctx_vision
-            ops.insert_prompt(self.vpt_rounded, self.params["vpt"], 1, n, 0, n, self.Dv, round_fp16=True)
+            ops.insert_prompt(self.vpt_rounded, self.vprompts[0], 1, n, 0, n, self.Dv, round_fp16=True)
             ops.layernorm_fwd(self.vpt_rounded, *self.ln_pre, self.vpt_scratch, *self.vpt_stats)
             ops.prompt_grad(self.vt.dx, self.vpt_gsum, B, self.Lv, 1 + cfg.arch.n_patches, n, self.Dv,
                             zero_rows=False, round_fp16=False)
-            ops.layernorm_bwd(self.vpt_gsum, self.vpt_rounded, self.ln_pre[0], *self.vpt_stats, self.grads["vpt"])
+            ops.layernorm_bwd(self.vpt_gsum, self.vpt_rounded, self.ln_pre[0], *self.vpt_stats, self.vgrads[0])
+            if cfg.coupling:
+                # d(text prompts) += d(vision prompts) . W ; dW, db of the coupling Linears (autograd of maple.py:199-204)
+                ops.small_linear_bwd(self.couple_x, self.couple_w, self.vis_prompt_grad, dx=self.couple_dx,
+                                     dw=self.couple_dw, db=self.couple_db, accumulate_dx=True)
         if multi:
             dist.all_reduce(self.flat_grad, group=cfg.process_group)
         return self.flat_grad
@@ -363,10 +463,29 @@ class PromptedClipStep:
     @torch.no_grad()
     def inference_logits(self, recompute_text=True):
         """Eval branch of CustomCLIP.forward (promptsrc.py:187-193, 212-213): logits [B, C]."""
+        if self.per_image:
+            self.image_features()
+            self.text_features()
+            return self.compute_logits()
         if recompute_text:
             self.text_features()
         self.image_features()
         return self.compute_logits()
+
+    @torch.no_grad()
+    def per_image_logits_for(self, image: torch.Tensor) -> torch.Tensor:
+        """CoCoOp evaluation (cocoop.py:235-260, eval branch): the text features depend on the image, so nothing
+        can be cached; test images are run in chunks of the configured batch through the step's own buffers."""
+        assert self.per_image
+        Bc, outs = self.cfg.batch, []
+        for lo in range(0, image.shape[0], Bc):
+            chunk = image[lo:lo + Bc]
+            b = chunk.shape[0]
+            self.image[:b].copy_(chunk)
+            if b < Bc:
+                self.image[b:].zero_()
+            outs.append(self.inference_logits()[:b].clone())
+        return outs[0] if len(outs) == 1 else torch.cat(outs, 0)
 
     def total_loss(self):
         return self.losses.sum()
@@ -456,6 +575,7 @@ class VisionInference:
     @torch.no_grad()
     def refresh_text(self):
         self.step.text_features()
+        self.step.couple_prompts()          # MaPLe: the vision prompts follow the text prompts
         self.text_valid = True
 
     @torch.no_grad()
@@ -474,11 +594,10 @@ class VisionInference:
                 self.image[b:].zero_()
             ops.im2col_patches(self.image, self.patches, a.image_resolution, a.vision_patch_size)
             ops.gemm(self.patches, st.conv_w, self.pe)
-            vpt = st.params["vpt"] if cfg.n_ctx_vision > 0 else None
+            vpt = st.vprompts[0] if cfg.n_ctx_vision > 0 else None
             ops.assemble_vision_tokens(self.pe, st.cls, st.vpos, vpt, *st.ln_pre, self.vt.x0, self.batch,
                                        a.n_patches, cfg.n_ctx_vision, st.Dv)
-            self.vt.forward({i: st.params[f"vision.{i}"] for i in range(1, cfg.depth_vision)}
-                            if cfg.n_ctx_vision > 0 else None)
+            self.vt.forward(st.vprompts if cfg.n_ctx_vision > 0 else None)
             ops.gather_ln_fwd(self.vt.x_final, None, *st.ln_post, self.hv, None, None, self.batch, self.vt.L, st.Dv)
             ops.gemm(self.hv, st.vproj_t, self.f)
             ops.l2norm_fwd(self.f, self.f_hat, None)

@@ -151,6 +151,17 @@ def make_maple_params(arch: ClipArch, n_ctx: int, depth: int, seed: int = 200) -
     return out
 
 
+def make_cocoop_params(arch: ClipArch, seed: int = 300) -> dict:
+    """CoCoOp's meta-net (trainers/cocoop.py:139-143): Linear(vis_dim, vis_dim // 16) -> ReLU -> Linear(.., ctx_dim),
+    nn.Linear default init scale.  Keys relative to `prompt_learner.`."""
+    g = torch.Generator().manual_seed(seed)
+    E, Dt = arch.embed_dim, arch.transformer_width
+    Hm = E // 16
+    u = lambda bound, *s: (torch.rand(*s, generator=g) * 2 - 1) * bound  # noqa: E731
+    return {"meta_net.linear1.weight": u(1 / math.sqrt(E), Hm, E), "meta_net.linear1.bias": u(1 / math.sqrt(E), Hm),
+            "meta_net.linear2.weight": u(1 / math.sqrt(Hm), Dt, Hm), "meta_net.linear2.bias": u(1 / math.sqrt(Hm), Dt)}
+
+
 # ------------------------------------------------------------------ tokens
 def load_token_fixture(name: str = "tokens_object1000") -> np.ndarray:
     """int32 [C,77] CLIP token ids of "a photo of a object {i}." produced by the reference tokenizer

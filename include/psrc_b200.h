@@ -181,6 +181,36 @@ int psrc_l2norm_fwd(const float* x, float* y, float* inv_norm, int rows, int D,
 int psrc_l2norm_bwd(const float* dy, const float* y, const float* inv_norm, float* dx,
                     int rows, int D, psrc_stream_t stream);
 
+/* ------------------------------------------ trainable small layers (MaPLe, CoCoOp)
+ * The only trainable dense layers on the path act on a handful of rows; fp32, batched over G
+ * independent (X, W, b) groups, all tensors contiguous:
+ *   X [G,R,K]  W [G,N,K]  b [G,N] (or NULL)  Y [G,R,N]
+ * MaPLe coupling functions (PromptSRC/trainers/maple.py:145 `proj`, :155-156
+ * `compound_prompt_projections`, applied at :199-204): G = prompt depth, R = n_ctx.
+ * CoCoOp meta-net (PromptSRC/trainers/cocoop.py:139-143, applied at :187): G = 1, R = images,
+ * linear1 with relu != 0, then linear2. */
+int psrc_small_linear_fwd(const float* X, const float* W, const float* b, float* Y,
+                          int G, int R, int N, int K, int relu, psrc_stream_t stream);
+/* autograd of the above: dW [G,N,K] = dY^T . X, db [G,N] = sum_r dY (both overwritten, skipped
+ * when dW == NULL), dX [G,R,K] (+)= dY . W (skipped when dX == NULL).  Y_relu != NULL: the layer
+ * ended in a ReLU whose OUTPUT is Y_relu; dY is masked by (Y_relu > 0) first. */
+int psrc_small_linear_bwd(const float* X, const float* W, const float* dY, const float* Y_relu,
+                          float* dX, int accumulate_dX, float* dW, float* db,
+                          int G, int R, int N, int K, psrc_stream_t stream);
+/* CoCoOp logits with one text-feature set per image (cocoop.py:246-255):
+ *   logits[b,c] = scale * <f_hat[b,:], t_hat[b,c,:]>,  t_hat [B,C,E]
+ * backward: d_that[b,c,:] = scale * d_logits[b,c] * f_hat[b,:] (the image tower is frozen, so no
+ * gradient w.r.t. f_hat is produced). */
+int psrc_group_logits_fwd(const float* f_hat, const float* t_hat, float* logits, int B, int C,
+                          int E, float scale, psrc_stream_t stream);
+int psrc_group_logits_bwd(const float* f_hat, const float* d_logits, float* d_that, int B, int C,
+                          int E, float scale, psrc_stream_t stream);
+/* autograd of `ctx_shifted = ctx[None] + bias[:,None]` (cocoop.py:185-188): gg [G,n_ctx,D] is the
+ * context-row gradient summed over the classes of image g (psrc_prompt_grad per image);
+ * dctx[j,:] = sum_g gg[g,j,:], dbias[g,:] = sum_j gg[g,j,:]. */
+int psrc_ctx_bias_grad(const float* gg, float* dctx, float* dbias, int G, int n_ctx, int D,
+                       psrc_stream_t stream);
+
 /* ------------------------------------------------------------------- loss
  * PromptSRC objective and its gradient in one pass (promptsrc.py:204, :304-324;
  * focal CE: coop.py:146-163 / promptsrc_pets_focal.py:93-117):

@@ -211,6 +211,28 @@ def maple_step(sd, tokens, image, label, ctx, compound_text, proj, compound_proj
     return {"loss": loss, "logits": logits}
 
 
+def cocoop_step(sd, tokens, image, label, ctx, meta, n_ctx, vision_heads, text_heads, focal_alpha=None,
+                use_focal=False, truncate=None):
+    """CoCoOp: PromptLearner.forward (trainers/cocoop.py:173-198) + CustomCLIP.forward (:235-260).
+    meta = (W1 [Hm, E], b1 [Hm], W2 [Dt, Hm], b2 [Dt]) is `meta_net` (:139-143); every image gets its own
+    context `ctx + meta_net(f_hat)` and therefore its own pass of the text encoder (:249-252)."""
+    w1, b1, w2, b2 = meta
+    emb = sd["token_embedding.weight"][tokens]
+    prefix, suffix = emb[:, :1], emb[:, 1 + n_ctx:]                 # cocoop.py:162-163
+    eot = tokens.argmax(-1)
+    f_hat = normalize(vision_tower(image, sd, vision_heads))        # :241-242
+    bias = torch.relu(f_hat @ w1.t() + b1) @ w2.t() + b2            # :185
+    scale = sd["logit_scale"].exp()
+    rows = []
+    for i in range(image.shape[0]):                                 # :249-252
+        prompts = construct_prompts(prefix, ctx + bias[i], suffix)  # :187-193
+        t_hat = normalize(text_tower(prompts, eot, sd, text_heads, truncate=truncate))
+        rows.append(scale * f_hat[i] @ t_hat.t())
+    logits = torch.stack(rows)                                      # :255
+    loss = focal_ce(logits, label, focal_alpha) if use_focal else F.cross_entropy(logits, label)
+    return {"loss": loss, "logits": logits}
+
+
 def sgd_step(params, grads, bufs, lr, momentum=0.9, weight_decay=5e-4):
     """torch.optim.SGD as built by dassl/optim/optimizer.py:105-113 (dampening 0, no nesterov)."""
     out_p, out_b = [], []

@@ -40,6 +40,9 @@ CASES = {
     # MaPLe hard-codes the ViT-B widths 768 / 512 (maple.py:144-156): full-size towers, few classes
     "vitb_maple_ce": ("MaPLe", "ViT-B/16", RAGGED_NAMES, 2, 3, {}),
     "vitb_maple_focal": ("MaPLe", "ViT-B/16", RAGGED_NAMES, 2, 3, {"TRAINER.MAPLE.USE_FOCAL_LOSS": True}),
+    # CoCoOp runs unmodified on CPU in fp32
+    "tiny_cocoop_ce": ("CoCoOp", "tiny", RAGGED_NAMES, 3, 0, {}),
+    "tiny_cocoop_focal": ("CoCoOp", "tiny", RAGGED_NAMES, 3, 0, {"TRAINER.COCOOP.USE_FOCAL_LOSS": True}),
 }
 
 
@@ -222,6 +225,53 @@ def run_maple(name, arch_name, classnames, batch, depth, extra):
     np.savez_compressed(os.path.join(GOLD, name + ".npz"), **fx)
 
 
+def run_cocoop(name, arch_name, classnames, batch, extra):
+    arch = S.ARCHS[arch_name]
+    sd = S.make_clip_state_dict(arch, seed=0)
+    n_ctx = 4
+    shots = S.lt_counts_cifar100(len(classnames), 50, 0.1)
+    over = {"INPUT.SIZE": (arch.image_resolution, arch.image_resolution), "TRAINER.COCOOP.N_CTX": n_ctx,
+            "TRAINER.COCOOP.CTX_INIT": "a photo of a", "TRAINER.COCOOP.PREC": "fp32",
+            "DATASET.PER_CLASS_SHOTS": shots}
+    over.update(extra)
+    cfg = H.make_cfg("CoCoOp", **over)
+    torch.manual_seed(17)
+    tm, model = H.build_reference_model("CoCoOp", cfg, classnames, sd)
+    H.freeze_like_trainer("CoCoOp", model)
+    with torch.no_grad():  # seeded meta-net, reproducible without the reference (synthetic.make_cocoop_params)
+        mp_ = S.make_cocoop_params(arch, seed=300)
+        named = dict(model.prompt_learner.named_parameters())
+        for k, v in mp_.items():
+            named[k].copy_(v)
+    image, label = S.synthetic_batch(batch, len(classnames), arch.image_resolution, seed=4)
+    tokens = model.tokenized_prompts.clone()
+    init = {n: p.detach().clone() for n, p in model.named_parameters() if p.requires_grad}
+    model.train()
+    opt = torch.optim.SGD([p for p in model.parameters() if p.requires_grad], lr=0.002, momentum=0.9, weight_decay=5e-4)
+    loss = model(image, label)                                      # cocoop.py:323
+    opt.zero_grad(); loss.backward(); opt.step()                    # :324-326
+    grads = {n: p.grad.detach().clone() for n, p in model.named_parameters() if p.requires_grad}
+    after = {n: p.detach().clone() for n, p in model.named_parameters() if p.requires_grad}
+    use_focal = bool(extra.get("TRAINER.COCOOP.USE_FOCAL_LOSS", False))
+    alpha = torch.tensor(S.focal_alpha(shots, len(classnames))) if use_focal else None
+    P = {n: t.clone().requires_grad_(True) for n, t in init.items()}
+    meta = tuple(P[f"prompt_learner.meta_net.{k}"] for k in ("linear1.weight", "linear1.bias", "linear2.weight",
+                                                              "linear2.bias"))
+    o = O.cocoop_step(sd, tokens, image, label, P["prompt_learner.ctx"], meta, n_ctx, arch.vision_heads,
+                      arch.transformer_heads, focal_alpha=alpha, use_focal=use_focal)
+    o["loss"].backward()
+    worst = min(cos(P[n].grad, grads[n]) for n in grads)
+    print(f"[{name}] reference loss={float(loss):.6f}; oracle |d|={abs(float(o['loss']) - float(loss)):.2e} "
+          f"worst grad cos={worst:.7f} trainable={sorted(grads)}")
+    assert abs(float(o["loss"]) - float(loss)) < 2e-5 and worst > 0.99999
+    fx = {"tokens": tokens.numpy().astype(np.int32), "label": label.numpy().astype(np.int32),
+          "loss": np.float32(float(loss)), "logits": o["logits"].detach().numpy(),
+          "shots": np.array(shots, dtype=np.int32), "n_ctx": np.int32(n_ctx)}
+    for n in grads:
+        fx["init/" + n], fx["grad/" + n], fx["after/" + n] = init[n].numpy(), grads[n].numpy(), after[n].numpy()
+    np.savez_compressed(os.path.join(GOLD, name + ".npz"), **fx)
+
+
 def write_token_fixtures():
     os.makedirs(S.DATA_DIR, exist_ok=True)
     toks = H.tokenize([f"a photo of a object {i}." for i in range(1000)]).numpy().astype(np.int32)
@@ -248,4 +298,6 @@ if __name__ == "__main__":
             run_coop(nm, arch_name, classnames, batch, extra)
         elif trainer == "MaPLe":
             run_maple(nm, arch_name, classnames, batch, depth, extra)
+        elif trainer == "CoCoOp":
+            run_cocoop(nm, arch_name, classnames, batch, extra)
     print("golden fixtures written to", GOLD)

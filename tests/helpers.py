@@ -57,6 +57,68 @@ def promptsrc_setup(arch_name, depth, tokens, device, prec, batch, sd=None, fixe
     return step, sd, fixed
 
 
+def maple_ref_name(key: str) -> str:
+    """MaPLe step key -> reference named_parameters key (maple.py:145-156)."""
+    if key == "ctx":
+        return "prompt_learner.ctx"
+    parts = key.split(".")
+    if parts[0] == "text":
+        return f"prompt_learner.compound_prompts_text.{int(parts[1]) - 1}"
+    kind = "weight" if parts[1] == "w" else "bias"
+    i = int(parts[2])
+    return f"prompt_learner.proj.{kind}" if i == 0 else f"prompt_learner.compound_prompt_projections.{i - 1}.{kind}"
+
+
+def maple_setup(arch_name, depth, tokens, device, prec, batch, n_ctx=2, sd=None, world=1, rank=0, pg=None,
+                focal_alpha=None, ctx_init=None):
+    """The MaPLe configuration of oracle/make_golden.py:run_maple: weights seed 0, coupling parameters seed 200,
+    ctx = embedding of the first n_ctx prompt words (maple.py:125-131)."""
+    from psrc_b200 import synthetic as S
+    from psrc_b200.step import PromptedClipStep, StepConfig
+    arch = S.ARCHS[arch_name]
+    sd = sd if sd is not None else S.make_clip_state_dict(arch, seed=0)
+    tokens = torch.as_tensor(np.asarray(tokens)).long()
+    cfg = StepConfig(arch=arch, n_cls=tokens.shape[0], batch=batch, prec=prec, n_ctx_text=n_ctx, n_ctx_vision=n_ctx,
+                     depth_text=depth, depth_vision=depth, coupling=True, world_size=world, rank=rank,
+                     process_group=pg, focal_alpha=focal_alpha)
+    step = PromptedClipStep(cfg, sd, tokens, device)
+    mp_ = S.make_maple_params(arch, n_ctx, depth, seed=200)
+    with torch.no_grad():
+        step.params["ctx"].copy_(ctx_init if ctx_init is not None
+                                 else sd["token_embedding.weight"][tokens[0, 1:1 + n_ctx]])
+        for k in step.params:
+            if k != "ctx":
+                step.params[k].copy_(mp_[maple_ref_name(k)[len("prompt_learner."):]])
+    return step, sd, mp_
+
+
+COCOOP_REF = {"ctx": "prompt_learner.ctx", "meta.w1": "prompt_learner.meta_net.linear1.weight",
+              "meta.b1": "prompt_learner.meta_net.linear1.bias", "meta.w2": "prompt_learner.meta_net.linear2.weight",
+              "meta.b2": "prompt_learner.meta_net.linear2.bias"}
+
+
+def cocoop_setup(arch_name, tokens, device, prec, batch, n_ctx=4, sd=None, world=1, rank=0, pg=None,
+                 focal_alpha=None):
+    """The CoCoOp configuration of oracle/make_golden.py:run_cocoop: weights seed 0, meta-net seed 300,
+    ctx = embedding of "a photo of a" (cocoop.py:124-131)."""
+    from psrc_b200 import synthetic as S
+    from psrc_b200.step import PromptedClipStep, StepConfig
+    arch = S.ARCHS[arch_name]
+    sd = sd if sd is not None else S.make_clip_state_dict(arch, seed=0)
+    tokens = torch.as_tensor(np.asarray(tokens)).long()
+    cfg = StepConfig(arch=arch, n_cls=tokens.shape[0], batch=batch, prec=prec, n_ctx_text=n_ctx, n_ctx_vision=0,
+                     depth_text=1, depth_vision=0, per_image_text=True, meta_hidden=arch.embed_dim // 16,
+                     world_size=world, rank=rank, process_group=pg, focal_alpha=focal_alpha)
+    step = PromptedClipStep(cfg, sd, tokens, device)
+    mp_ = S.make_cocoop_params(arch, seed=300)
+    with torch.no_grad():
+        step.params["ctx"].copy_(sd["token_embedding.weight"][tokens[0, 1:1 + n_ctx]])
+        for k in step.params:
+            if k != "ctx":
+                step.params[k].copy_(mp_[COCOOP_REF[k][len("prompt_learner."):]])
+    return step, sd, mp_
+
+
 # ---------------------------------------------------------------------------------------------
 class FakeKernels:
     """Replaces psrc_b200.ops.* with shape/dtype-checking no-ops that work on CPU tensors, so the host
@@ -72,8 +134,35 @@ class FakeKernels:
         for name in ("gemm", "gemm_f32_strided", "layernorm_fwd", "layernorm_bwd", "attn_fwd", "attn_bwd",
                      "im2col_patches", "assemble_vision_tokens", "assemble_text_prompts", "insert_prompt",
                      "prompt_grad", "gather_ln_fwd", "gather_ln_bwd", "l2norm_fwd", "l2norm_bwd", "loss_fwd_bwd",
-                     "sgd_step", "cast", "axpy"):
+                     "sgd_step", "cast", "axpy", "small_linear_fwd", "small_linear_bwd", "group_logits_fwd",
+                     "group_logits_bwd", "ctx_bias_grad"):
             monkeypatch.setattr(ops, name, getattr(self, name))
+
+    def small_linear_fwd(self, x, w, b, y, relu=False):
+        self._rec("small_linear_fwd")
+        G, R, K = x.shape
+        assert w.shape[0] == G and w.shape[2] == K and y.shape == (G, R, w.shape[1])
+        return y
+
+    def small_linear_bwd(self, x, w, dy, dx=None, dw=None, db=None, y_relu=None, accumulate_dx=False):
+        self._rec("small_linear_bwd")
+        assert dy.shape == (x.shape[0], x.shape[1], w.shape[1])
+        assert dx is None or dx.shape == x.shape
+        assert dw is None or dw.shape == w.shape
+
+    def group_logits_fwd(self, f_hat, t_hat, logits, scale):
+        self._rec("group_logits_fwd")
+        assert t_hat.shape == (logits.numel(), f_hat.shape[1])
+        return logits
+
+    def group_logits_bwd(self, f_hat, d_logits, d_that, scale):
+        self._rec("group_logits_bwd")
+        assert d_that.shape == (d_logits.numel(), f_hat.shape[1])
+        return d_that
+
+    def ctx_bias_grad(self, gg, dctx, dbias):
+        self._rec("ctx_bias_grad")
+        assert dctx.shape == gg.shape[1:] and dbias.shape == (gg.shape[0], gg.shape[2])
 
     def _rec(self, name):
         self.calls.append(name)

@@ -395,7 +395,55 @@ def check_loss(res: Results):
     res.add("loss CE only value", abs(float(losses[0]) - float(F.cross_entropy(logits, labels).detach())), 1e-5)
 
 
+# ----------------------------------------------------------------------------- MaPLe / CoCoOp small layers
+def check_small_layers(res: Results):
+    from psrc_b200 import ops
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(5)
+    rn = lambda *s: torch.randn(*s, device=dev, generator=g)  # noqa: E731
+    for tag, (G, R, N, K, relu) in {"maple coupling 9x[2,512]->768": (9, 2, 768, 512, False),
+                                     "cocoop linear1 [128,512]->32 relu": (1, 128, 32, 512, True),
+                                     "cocoop linear2 [128,32]->512": (1, 128, 512, 32, False),
+                                     "ragged [3,5,50]->37": (3, 5, 37, 50, True)}.items():
+        x, w, b = rn(G, R, K), rn(G, N, K) * 0.1, rn(G, N)
+        y = torch.empty(G, R, N, device=dev)
+        ops.small_linear_fwd(x, w, b, y, relu=relu)
+        ref = torch.einsum("grk,gnk->grn", x, w) + b[:, None]
+        ref = ref.clamp_min(0) if relu else ref
+        res.add(f"small_linear_fwd {tag}", rel_err(y, ref), 1e-5)
+        dy = rn(G, R, N)
+        d = dy * (ref > 0) if relu else dy
+        dx0 = rn(G, R, K)
+        dx, dw, db = dx0.clone(), torch.empty_like(w), torch.empty_like(b)
+        ops.small_linear_bwd(x, w, dy, dx=dx, dw=dw, db=db, y_relu=y if relu else None, accumulate_dx=True)
+        res.add(f"small_linear_bwd dX(+=) {tag}", rel_err(dx, dx0 + torch.einsum("grn,gnk->grk", d, w)), 1e-5)
+        res.add(f"small_linear_bwd dW {tag}", rel_err(dw, torch.einsum("grn,grk->gnk", d, x)), 1e-5)
+        res.add(f"small_linear_bwd db {tag}", rel_err(db, d.sum(1)), 1e-5)
+    B, Cn, E = 7, 365, 512
+    f, t = rn(B, E), rn(B * Cn, E)
+    logits = torch.empty(B, Cn, device=dev)
+    ops.group_logits_fwd(f, t, logits, 14.3)
+    res.add("group_logits_fwd", rel_err(logits, 14.3 * torch.einsum("be,bce->bc", f, t.view(B, Cn, E))), 1e-5)
+    dl, dt = rn(B, Cn), torch.empty(B * Cn, E, device=dev)
+    ops.group_logits_bwd(f, dl, dt, 14.3)
+    res.add("group_logits_bwd", rel_err(dt.view(B, Cn, E), 14.3 * dl[:, :, None] * f[:, None, :]), 1e-6)
+    gg = rn(B, 4, E)
+    dctx, dbias = torch.empty(4, E, device=dev), torch.empty(B, E, device=dev)
+    ops.ctx_bias_grad(gg, dctx, dbias)
+    res.add("ctx_bias_grad dctx", rel_err(dctx, gg.sum(0)), 1e-6)
+    res.add("ctx_bias_grad dbias", rel_err(dbias, gg.sum(1)), 1e-6)
+    # grouped context assembly (cocoop.py:185-198): sequence s = g*C + c gets ctx + bias[g]
+    C2, L, n_ctx, D = 6, 9, 4, 64
+    prefix, suffix, ctx, pos, bias = rn(C2, 1, D), rn(C2, 12, D), rn(n_ctx, D), rn(77, D), rn(B, D)
+    x = torch.empty(B * C2 * L, D, device=dev)
+    ops.assemble_text_prompts(prefix, suffix, ctx, pos, x, C2, L, n_ctx, D, ctx_bias=bias, n_groups=B)
+    ref = torch.stack([torch.cat([prefix, (ctx + bias[i]).expand(C2, n_ctx, D), suffix], 1)[:, :L] + pos[:L]
+                       for i in range(B)])
+    res.add("assemble_text_prompts grouped (+bias)", max_err(x.view(B, C2, L, D), ref), 1e-6)
+
+
 GROUPS = {
+    "small_layers": check_small_layers,
     "gemm_simt": lambda r: check_gemm(r, "simt"),
     "gemm_tc": lambda r: check_gemm(r, "tc"),
     "gemm_strided": check_gemm_strided,

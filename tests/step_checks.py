@@ -18,7 +18,8 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
     if p not in sys.path:
         sys.path.insert(0, p)
 
-from helpers import cos, load_golden, promptsrc_setup, ref_name  # noqa: E402
+from helpers import (COCOOP_REF, cocoop_setup, cos, load_golden, maple_ref_name, maple_setup,  # noqa: E402
+                     promptsrc_setup, ref_name)
 
 CASES = {"tiny_promptsrc": ("tiny", 3), "cfg1_promptsrc": ("ViT-B/16", 9)}
 # BASELINE.json tolerances, stated for the ViT-B/16 configs: fp32 mode 1e-4 on logits, bf16 2e-2, gradient cosine 0.999.
@@ -93,6 +94,100 @@ def run_promptsrc_case(name: str, prec: str, sgd: bool = True) -> dict:
     return m
 
 
+def _generic_metrics(step, fx, name_of, lr, dev, sampled=False):
+    """logits / loss / per-tensor gradient cosines / parameters after the reference's SGD step."""
+    from psrc_b200 import ops
+    m = {}
+    m["logits_maxabs"] = float((step.logits.cpu() - torch.from_numpy(fx["logits"])).abs().max())
+    loss = float(step.losses.sum())
+    m["loss"], m["loss_rel"] = loss, abs(loss - float(fx["loss"])) / abs(float(fx["loss"]))
+    worst, worst_key, ours, refs = 2.0, None, [], []
+    for k in step.params:
+        n = name_of(k)
+        g = step.grads[k].cpu()
+        if "grad/" + n in fx:
+            r = torch.from_numpy(fx["grad/" + n])
+        else:                              # coupling matrices: every 8th row is in the fixture
+            g, r = g[::8], torch.from_numpy(fx["grad8/" + n])
+        c = cos(g, r)
+        m[f"gradcos/{k}"] = c
+        ours.append(g.flatten()), refs.append(r.flatten())
+        if c < worst:
+            worst, worst_key = c, k
+    m["gradcos_worst"], m["gradcos_worst_key"] = worst, worst_key
+    m["gradcos_all"] = cos(torch.cat(ours), torch.cat(refs))
+    buf = torch.zeros_like(step.flat_param)
+    before = {k: step.params[k].detach().cpu().clone() for k in step.params}
+    ops.sgd_step(step.flat_param, step.flat_grad, buf, torch.tensor([lr], device=dev), 0.9, 0.0, 5e-4, False, True)
+    torch.cuda.synchronize()
+    du, dr = [], []
+    for k in step.params:
+        n = name_of(k)
+        a = step.params[k].cpu()
+        if "after/" + n in fx:
+            r, b0 = torch.from_numpy(fx["after/" + n]), before[k]
+        else:
+            a, r, b0 = a[::8], torch.from_numpy(fx["after8/" + n]), before[k][::8]
+        du.append((a - b0).flatten()), dr.append((r - b0).flatten())
+    m["param_update_cos"] = cos(torch.cat(du), torch.cat(dr))
+    return m
+
+
+def run_maple_case(name: str, prec: str) -> dict:
+    """MaPLe ViT-B/16 (the reference hard-codes these widths) against tests/golden/vitb_maple_*.npz."""
+    from psrc_b200 import synthetic as S
+    fx = load_golden(name)
+    dev, arch = "cuda", S.ARCHS["ViT-B/16"]
+    B, C = fx["label"].shape[0], fx["tokens"].shape[0]
+    alpha = S.focal_alpha(fx["shots"].tolist(), C) if name.endswith("focal") else None
+    step, sd, _ = maple_setup("ViT-B/16", int(fx["depth"]), fx["tokens"], dev, prec, batch=B, n_ctx=int(fx["n_ctx"]),
+                              focal_alpha=alpha, ctx_init=torch.from_numpy(fx["init/prompt_learner.ctx"]))
+    image, label = S.synthetic_batch(B, C, arch.image_resolution, seed=3)
+    assert np.array_equal(label.numpy().astype(np.int32), fx["label"])
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    torch.cuda.synchronize()
+    return _generic_metrics(step, fx, maple_ref_name, 0.0035, dev)
+
+
+def run_cocoop_case(name: str, prec: str) -> dict:
+    """CoCoOp (tiny architecture) against tests/golden/tiny_cocoop_*.npz."""
+    from psrc_b200 import synthetic as S
+    fx = load_golden(name)
+    dev, arch = "cuda", S.ARCHS["tiny"]
+    B, C = fx["label"].shape[0], fx["tokens"].shape[0]
+    alpha = S.focal_alpha(fx["shots"].tolist(), C) if name.endswith("focal") else None
+    step, sd, _ = cocoop_setup("tiny", fx["tokens"], dev, prec, batch=B, n_ctx=int(fx["n_ctx"]), focal_alpha=alpha)
+    image, label = S.synthetic_batch(B, C, arch.image_resolution, seed=4)
+    assert np.array_equal(label.numpy().astype(np.int32), fx["label"])
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    torch.cuda.synchronize()
+    return _generic_metrics(step, fx, lambda k: COCOOP_REF[k], 0.002, dev)
+
+
+def check_generic(m: dict, prec: str, name: str = "") -> list[str]:
+    t = TOL_TINY_BF16 if (prec == "bf16" and name.startswith("tiny")) else TOL[prec]
+    bad = []
+    if m["logits_maxabs"] > t["logits"]:
+        bad.append(f"logits max|d| {m['logits_maxabs']:.3e} > {t['logits']}")
+    if m["loss_rel"] > t["loss"]:
+        bad.append(f"loss rel {m['loss_rel']:.3e} > {t['loss']}")
+    if m["gradcos_worst"] < t["cos"]:
+        bad.append(f"grad cosine {m['gradcos_worst']:.6f} ({m['gradcos_worst_key']}) < {t['cos']}")
+    if m["gradcos_all"] < t["cos_all"]:
+        bad.append(f"concatenated gradient cosine {m['gradcos_all']:.6f} < {t['cos_all']}")
+    if m["param_update_cos"] < t["cos"]:
+        bad.append(f"SGD update cosine {m['param_update_cos']:.6f} < {t['cos']}")
+    return bad
+
+
+OTHER_CASES = {"vitb_maple_ce": run_maple_case, "vitb_maple_focal": run_maple_case,
+               "tiny_cocoop_ce": run_cocoop_case, "tiny_cocoop_focal": run_cocoop_case}
+
+
 def check(m: dict, prec: str, name: str = "") -> list[str]:
     t = TOL_TINY_BF16 if (prec == "bf16" and name.startswith("tiny")) else TOL[prec]
     bad = []
@@ -122,8 +217,19 @@ def check(m: dict, prec: str, name: str = "") -> list[str]:
 
 if __name__ == "__main__":
     names = [a for a in sys.argv[1:] if a in CASES] or list(CASES)
+    others = [a for a in sys.argv[1:] if a in OTHER_CASES] or ([] if names != list(CASES) else list(OTHER_CASES))
     precs = [a for a in sys.argv[1:] if a in TOL] or ["fp32", "bf16"]
     rc = 0
+    for n in others:
+        for p in precs:
+            m = OTHER_CASES[n](n, p)
+            bad = check_generic(m, p, n)
+            print(f"===== {n} [{p}] {'PASS' if not bad else 'FAIL: ' + '; '.join(bad)}")
+            for k, v in m.items():
+                print(f"   {k:32s} {v}")
+            rc |= bool(bad)
+    if others and not [a for a in sys.argv[1:] if a in CASES] and sys.argv[1:]:
+        sys.exit(rc)
     for n in names:
         for p in precs:
             m = run_promptsrc_case(n, p)

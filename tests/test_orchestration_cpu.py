@@ -11,10 +11,11 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from helpers import cos, load_golden, promptsrc_setup, ref_name
+from helpers import COCOOP_REF, cocoop_setup, cos, load_golden, maple_ref_name, maple_setup, promptsrc_setup, ref_name
 from torch_kernels import TorchKernels
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
 
 class _Patch:
@@ -44,6 +45,63 @@ def test_step_orchestration_matches_reference_golden(monkeypatch):
     assert np.array_equal(step.logits.argmax(1).numpy().astype(np.int32), fx["argmax"])
     for k in step.params:
         assert cos(step.grads[k], fx["grad/" + ref_name(k)]) > 0.99999, k
+
+
+@pytest.mark.parametrize("name,focal", [("tiny_cocoop_ce", False), ("tiny_cocoop_focal", True)])
+def test_cocoop_step_orchestration_matches_reference_golden(monkeypatch, name, focal):
+    """CoCoOp: meta-net -> per-image context shift -> B x C text sequences -> per-image logits, and the backward into
+    ctx + meta-net, against the unmodified reference's outputs (cocoop.py:173-198, :235-260)."""
+    TorchKernels().install(monkeypatch)
+    from psrc_b200 import synthetic as S
+    fx = load_golden(name)
+    B, C = fx["label"].shape[0], fx["tokens"].shape[0]
+    alpha = S.focal_alpha(fx["shots"].tolist(), C) if focal else None
+    step, sd, _ = cocoop_setup("tiny", fx["tokens"], "cpu", "fp32", batch=B, focal_alpha=alpha)
+    for k in step.params:
+        assert float((step.params[k] - torch.from_numpy(fx["init/" + COCOOP_REF[k]])).abs().max()) == 0.0, k
+    image, label = S.synthetic_batch(B, C, 64, seed=4)
+    assert np.array_equal(label.numpy().astype(np.int32), fx["label"])
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    assert float((step.logits - torch.from_numpy(fx["logits"])).abs().max()) < 1e-4
+    assert abs(float(step.losses.sum()) - float(fx["loss"])) < 2e-5
+    for k in step.params:
+        assert cos(step.grads[k], fx["grad/" + COCOOP_REF[k]]) > 0.99999, k
+    step.init_optimizer(lr=0.002)
+    step.sgd()
+    for k in step.params:
+        assert float((step.params[k] - torch.from_numpy(fx["after/" + COCOOP_REF[k]])).abs().max()) < 1e-6, k
+
+
+@pytest.mark.parametrize("focal", [False, True])
+def test_maple_step_orchestration_matches_oracle(monkeypatch, focal):
+    """MaPLe on the tiny architecture: coupled vision prompts (one batched Linear launch), prompt-only backward through
+    both towers and the coupling Linears, against the oracle restatement (pinned on the reference at ViT-B widths,
+    tests/golden/vitb_maple_*.npz -- the reference hard-codes 768/512)."""
+    import clip_oracle as O
+    TorchKernels().install(monkeypatch)
+    from psrc_b200 import synthetic as S
+    arch = S.ARCHS["tiny"]
+    depth, n_ctx, B = 3, 2, 3
+    tokens = S.synthetic_tokens(10, name_lens=[1, 2, 3, 8, 1, 1, 2, 2, 1, 2])
+    C = tokens.shape[0]
+    alpha = S.focal_alpha(list(range(1, C + 1)), C) if focal else None
+    step, sd, mp_ = maple_setup("tiny", depth, tokens, "cpu", "fp32", batch=B, focal_alpha=alpha)
+    image, label = S.synthetic_batch(B, C, arch.image_resolution, seed=3)
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    P = {k: step.params[k].detach().clone().requires_grad_(True) for k in step.params}
+    o = O.maple_step(sd, torch.as_tensor(tokens), image, label, P["ctx"], [P[f"text.{i}"] for i in range(1, depth)],
+                     (P["couple.w.0"], P["couple.b.0"]),
+                     [(P[f"couple.w.{i}"], P[f"couple.b.{i}"]) for i in range(1, depth)], n_ctx, arch.vision_heads,
+                     arch.transformer_heads, focal_alpha=torch.tensor(alpha) if focal else None, use_focal=focal)
+    o["loss"].backward()
+    assert float((step.logits - o["logits"].detach()).abs().max()) < 1e-4
+    assert abs(float(step.losses.sum()) - float(o["loss"])) < 2e-5
+    for k in step.params:
+        assert cos(step.grads[k], P[k].grad) > 0.99999, k
 
 
 def _free_port():

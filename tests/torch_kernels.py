@@ -54,7 +54,8 @@ def _fp16(x):
 class TorchKernels:
     NAMES = ("gemm", "gemm_f32_strided", "layernorm_fwd", "layernorm_bwd", "attn_fwd", "attn_bwd", "im2col_patches",
              "assemble_vision_tokens", "assemble_text_prompts", "insert_prompt", "prompt_grad", "gather_ln_fwd",
-             "gather_ln_bwd", "l2norm_fwd", "l2norm_bwd", "loss_fwd_bwd", "sgd_step", "cast", "axpy")
+             "gather_ln_bwd", "l2norm_fwd", "l2norm_bwd", "loss_fwd_bwd", "sgd_step", "cast", "axpy",
+             "small_linear_fwd", "small_linear_bwd", "group_logits_fwd", "group_logits_bwd", "ctx_bias_grad")
 
     def install(self, monkeypatch):
         from psrc_b200 import ops
@@ -260,3 +261,39 @@ class TorchKernels:
     def axpy(y, x, a=1.0):
         y.add_(x, alpha=a)
         return y
+
+    # ---------------------------------------------------------------- trainable small layers (MaPLe, CoCoOp)
+    @staticmethod
+    def small_linear_fwd(x, w, b, y, relu=False):
+        o = torch.einsum("grk,gnk->grn", x, w)
+        if b is not None:
+            o = o + b[:, None]
+        y.copy_(o.clamp_min(0) if relu else o)
+        return y
+
+    @staticmethod
+    def small_linear_bwd(x, w, dy, dx=None, dw=None, db=None, y_relu=None, accumulate_dx=False):
+        d = dy if y_relu is None else dy * (y_relu > 0)
+        if dw is not None:
+            dw.copy_(torch.einsum("grn,grk->gnk", d, x))
+            db.copy_(d.sum(1))
+        if dx is not None:
+            g = torch.einsum("grn,gnk->grk", d, w)
+            dx.copy_(dx + g if accumulate_dx else g)
+
+    @staticmethod
+    def group_logits_fwd(f_hat, t_hat, logits, scale):
+        B, E = f_hat.shape
+        logits.copy_(scale * torch.einsum("be,bce->bc", f_hat, t_hat.view(B, -1, E)))
+        return logits
+
+    @staticmethod
+    def group_logits_bwd(f_hat, d_logits, d_that, scale):
+        B, E = f_hat.shape
+        d_that.copy_((scale * d_logits[:, :, None] * f_hat[:, None, :]).reshape(-1, E))
+        return d_that
+
+    @staticmethod
+    def ctx_bias_grad(gg, dctx, dbias):
+        dctx.copy_(gg.sum(0))
+        dbias.copy_(gg.sum(1))
