@@ -4,10 +4,12 @@
 label=None)`, attributes `prompt_learner / tokenized_prompts / image_encoder / text_encoder / logit_scale /
 dtype`, state-dict keys) and the trainers keep the Dassl `TrainerX` hooks (`check_cfg`, `build_model`,
 `forward_backward`, `model_inference`, `parse_batch_train`, `load_model`), registered under the reference's
-names so `train.py --trainer PromptSRC|CoOp` selects them:
+names so `train.py --trainer PromptSRC|MaPLe|CoOp|CoCoOp` selects them:
 
     PromptSRC   PromptSRC/trainers/promptsrc.py:170-213 (CustomCLIP), :216-420 (trainer)
     CoOp        PromptSRC/trainers/coop.py:302-390 (CustomCLIP), :396-500 (trainer)
+    MaPLe       PromptSRC/trainers/maple.py:111-255 (prompt learner, CustomCLIP), :257-357 (trainer)
+    CoCoOp      PromptSRC/trainers/cocoop.py:103-260 (prompt learner, CustomCLIP), :262-372 (trainer)
 
 All arithmetic runs in the sm_100a kernels through `step.PromptedClipStep`; there is no PyTorch fallback.
 The trainable prompt tensors are the reference's own `nn.Parameter`s (same names), re-pointed at views of the
@@ -304,6 +306,7 @@ class _Bridge(torch.autograd.Function):
         st.image.copy_(image)
         st.forward_train()
         ctx.model = model
+        ctx.set_materialize_grads(False)      # unused outputs arrive as None, not as zero tensors
         return st.logits.clone(), st.t_hat.clone(), st.f_hat.clone()
 
     @staticmethod
@@ -316,6 +319,20 @@ class _Bridge(torch.autograd.Function):
 class _CustomCLIPBase(nn.Module):
     """Shared machinery of the CustomCLIP variants: builds the kernel step from a reference-keyed CLIP module,
     binds the prompt nn.Parameters to the flat buffers, provides the fused / bridged / eval paths."""
+
+    def _make_prompt_learner(self, scfg, ctx_init, prefix, suffix, tokens):
+        return _PromptLearner(ctx_init.float(), prefix, suffix, tokens)
+
+    def _named_for_step(self, scfg):
+        """[(step key, reference-named nn.Parameter)] in the order of the step's flat buffer."""
+        named = [("ctx", self.prompt_learner.ctx)]
+        for i in range(1, scfg.depth_text):
+            named.append((f"text.{i}", self.text_encoder.transformer.resblocks[i].VPT_shallow))
+        if scfg.n_ctx_vision > 0:
+            named.append(("vpt", self.image_encoder.VPT))
+            for i in range(1, scfg.depth_vision):
+                named.append((f"vision.{i}", self.image_encoder.transformer.resblocks[i].VPT_shallow))
+        return named
 
     def _build(self, cfg, clip_model, tokens, step_kwargs, ctx_init, fixed_embeddings=None, device=None):
         dev = torch.device(device if device is not None else "cuda")
@@ -339,7 +356,8 @@ class _CustomCLIPBase(nn.Module):
         self._eager_steps = 0
         emb = sd["token_embedding.weight"][tokens]
         n_ctx = scfg.n_ctx_text
-        self.prompt_learner = _PromptLearner(ctx_init.float(), emb[:, :1].clone(), emb[:, 1 + n_ctx:].clone(), tokens)
+        self.prompt_learner = self._make_prompt_learner(scfg, ctx_init, emb[:, :1].clone(), emb[:, 1 + n_ctx:].clone(),
+                                                        tokens)
         self.tokenized_prompts = tokens
         self.image_encoder = clip_model.visual
         self.text_encoder = _TextEncoder(clip_model)
@@ -349,13 +367,7 @@ class _CustomCLIPBase(nn.Module):
         self.to(dev)
         # ---- bind the reference-named prompt parameters to the flat buffers
         st = self._step
-        named = [("ctx", self.prompt_learner.ctx)]
-        for i in range(1, scfg.depth_text):
-            named.append((f"text.{i}", self.text_encoder.transformer.resblocks[i].VPT_shallow))
-        if scfg.n_ctx_vision > 0:
-            named.append(("vpt", self.image_encoder.VPT))
-            for i in range(1, scfg.depth_vision):
-                named.append((f"vision.{i}", self.image_encoder.transformer.resblocks[i].VPT_shallow))
+        named = self._named_for_step(scfg)
         assert [k for k, _ in named] == list(st.params), (list(st.params), [k for k, _ in named])
         with torch.no_grad():
             for k, p in named:
@@ -375,10 +387,19 @@ class _CustomCLIPBase(nn.Module):
             self._infer.text_valid = False       # prompts may change between evaluations
         return super().train(mode)
 
+    def _is_inference(self, label):
+        """Dassl's `set_model_mode("eval")` reaches only the REGISTERED module -- for CoOp / CoCoOp that is
+        `prompt_learner` (coop.py:431, cocoop.py:304), so `self.training` stays True during `test()`.  The reference
+        then returns logits because `label is None`; `model_inference` runs under `torch.no_grad()`
+        (dassl/engine/trainer.py:445-449), which is what selects the forward-only path here."""
+        return (not self.training) or (label is None and not torch.is_grad_enabled())
+
     def _bridged(self, image):
         return _Bridge.apply(self, image, *self.prompt_parameters())
 
     def _eval_logits(self, image):
+        if self._step.per_image:                 # CoCoOp: text features depend on the image, nothing to cache
+            return self._step.per_image_logits_for(image.float())
         if self._infer is None:
             self._infer = VisionInference(self._step, self._test_batch)
         return self._infer.logits_for(image.float())
@@ -519,13 +540,170 @@ class CoOpCustomCLIP(_CustomCLIPBase):
         return self._bridged(image.float())[0]
 
     def forward(self, img1, lbl=None, img2=None):
-        if not self.training:
+        if self._is_inference(lbl):
             return self._eval_logits(img1)
         logits = self.forward_once(img1)
         if lbl is None:
             return logits
         st = self._step
         return F.cross_entropy(logits, lbl) if st.focal_alpha is None else _focal(logits, lbl, st)
+
+
+
+class _MaPLePromptLearner(nn.Module):
+    """MultiModalPromptLearner (maple.py:111-204): `ctx`, the coupling `proj`, the deeper text prompts and one
+    coupling Linear per deeper layer -- same attribute / state-dict names.  The reference hard-codes the ViT-B widths
+    (768, 512); here they follow the CLIP model (so ViT-L/14 works).  `forward()` returns the reference's
+    4-tuple with plain torch ops (external callers only; the training step runs the batched kernel)."""
+
+    def __init__(self, ctx, vis_width, depth, token_prefix, token_suffix, tokenized_prompts):
+        super().__init__()
+        import copy
+        n_ctx, ctx_dim = ctx.shape
+        self.proj = nn.Linear(ctx_dim, vis_width)                               # maple.py:144 (kept fp32, SURVEY F6)
+        self.ctx = nn.Parameter(ctx)
+        self.compound_prompts_text = nn.ParameterList(
+            [nn.Parameter(torch.empty(n_ctx, ctx_dim)) for _ in range(depth - 1)])   # :149-151
+        for p_ in self.compound_prompts_text:
+            nn.init.normal_(p_, std=0.02)
+        single = nn.Linear(ctx_dim, vis_width)
+        self.compound_prompt_projections = nn.ModuleList([copy.deepcopy(single) for _ in range(depth - 1)])  # :155-156
+        self.register_buffer("token_prefix", token_prefix)
+        self.register_buffer("token_suffix", token_suffix)
+        self.tokenized_prompts = tokenized_prompts
+        self.n_cls, self.n_ctx, self.compound_prompts_depth = token_prefix.shape[0], n_ctx, depth
+
+    def forward(self):
+        ctx = self.ctx.unsqueeze(0).expand(self.n_cls, -1, -1)
+        prompts = torch.cat([self.token_prefix, ctx, self.token_suffix], dim=1)
+        visual = [layer(self.compound_prompts_text[i]) for i, layer in enumerate(self.compound_prompt_projections)]
+        return prompts, self.proj(self.ctx), self.compound_prompts_text, visual
+
+
+class MaPLeCustomCLIP(_CustomCLIPBase):
+    """CustomCLIP of trainers/maple.py:206-255 (CE or focal loss, :221-238)."""
+
+    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None):
+        super().__init__()
+        T = cfg.TRAINER.MAPLE
+        self.cfg = cfg
+        depth = int(T.PROMPT_DEPTH)
+        assert depth >= 1, "PROMPT_DEPTH must be >= 1"                          # maple.py:122
+        n_ctx, ctx_init = int(T.N_CTX), _get(T, "CTX_INIT", "")
+        names = [n.replace("_", " ") for n in classnames]
+        sd_emb = clip_model.state_dict()["token_embedding.weight"].detach().float().cpu()
+        if ctx_init and n_ctx <= 4:                                             # :127-133
+            prefix_words = ctx_init.replace("_", " ")
+        else:
+            prefix_words = " ".join(["X"] * n_ctx)
+        if tokenized_prompts is None:
+            tokenized_prompts = _reference_tokenize([prefix_words + " " + n + "." for n in names])
+        tokens = torch.as_tensor(tokenized_prompts).long().cpu()
+        if ctx_init and n_ctx <= 4:
+            ctx_vectors = sd_emb[tokens[0, 1:1 + n_ctx]].clone()
+        else:
+            ctx_vectors = torch.empty(n_ctx, sd_emb.shape[1])
+            nn.init.normal_(ctx_vectors, std=0.02)
+        self.use_focal_loss = bool(_get(T, "USE_FOCAL_LOSS", False))
+        kw = dict(prec_cfg=T.PREC, n_ctx_text=n_ctx, n_ctx_vision=n_ctx, depth_text=depth, depth_vision=depth,
+                  coupling=True, zero_shot_branch=False)
+        if self.use_focal_loss:
+            kw["focal_alpha"] = _focal_alpha_from_cfg(cfg, len(classnames))
+        self._build(cfg, clip_model, tokens, kw, ctx_vectors, device=device)
+
+    def _make_prompt_learner(self, scfg, ctx_init, prefix, suffix, tokens):
+        return _MaPLePromptLearner(ctx_init.float(), scfg.arch.vision_width, scfg.depth_text, prefix, suffix, tokens)
+
+    def _named_for_step(self, scfg):
+        pl, d = self.prompt_learner, scfg.depth_text
+        named = [("ctx", pl.ctx)] + [(f"text.{i}", pl.compound_prompts_text[i - 1]) for i in range(1, d)]
+        lin = [pl.proj] + list(pl.compound_prompt_projections)
+        named += [(f"couple.w.{i}", lin[i].weight) for i in range(d)]
+        named += [(f"couple.b.{i}", lin[i].bias) for i in range(d)]
+        return named
+
+    def forward(self, image, label=None):
+        if self._is_inference(label):
+            return self._eval_logits(image)
+        logits = self._bridged(image.float())[0]
+        if label is None:
+            return logits                                                       # maple.py:252-255
+        st = self._step
+        return F.cross_entropy(logits, label) if st.focal_alpha is None else _focal(logits, label, st)
+
+
+class _CoCoOpPromptLearner(nn.Module):
+    """PromptLearner of trainers/cocoop.py:103-198: `ctx` + `meta_net` (linear1 -> ReLU -> linear2), same names.
+    `forward(im_features)` returns the [B, C, 77, D] instance-conditioned prompts with torch ops (external callers
+    only -- the training step never materialises them: the context shift is applied inside the assembly kernel)."""
+
+    def __init__(self, ctx, vis_dim, token_prefix, token_suffix, tokenized_prompts):
+        super().__init__()
+        ctx_dim = ctx.shape[1]
+        self.ctx = nn.Parameter(ctx)
+        self.meta_net = nn.Sequential(OrderedDict([("linear1", nn.Linear(vis_dim, vis_dim // 16)),
+                                                   ("relu", nn.ReLU(inplace=True)),
+                                                   ("linear2", nn.Linear(vis_dim // 16, ctx_dim))]))   # :139-143
+        self.register_buffer("token_prefix", token_prefix)
+        self.register_buffer("token_suffix", token_suffix)
+        self.tokenized_prompts = tokenized_prompts
+        self.n_cls, self.n_ctx = token_prefix.shape[0], ctx.shape[0]
+
+    def forward(self, im_features):
+        ctx_shifted = self.ctx.unsqueeze(0) + self.meta_net(im_features).unsqueeze(1)       # :185-188
+        return torch.stack([torch.cat([self.token_prefix, c.unsqueeze(0).expand(self.n_cls, -1, -1),
+                                       self.token_suffix], dim=1) for c in ctx_shifted], dim=0)
+
+
+class CoCoOpCustomCLIP(_CustomCLIPBase):
+    """CustomCLIP of trainers/cocoop.py:200-260 (CE or focal loss, :214-233).  The meta-net stays fp32 whatever
+    PREC says (the reference's `.half()` at :146-147 cannot run on its fp32 model)."""
+
+    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None):
+        super().__init__()
+        T = cfg.TRAINER.COCOOP
+        self.cfg = cfg
+        n_ctx, ctx_init = int(T.N_CTX), _get(T, "CTX_INIT", "")
+        names = [n.replace("_", " ") for n in classnames]
+        sd_emb = clip_model.state_dict()["token_embedding.weight"].detach().float().cpu()
+        if ctx_init:                                                            # cocoop.py:122-131
+            ctx_init = ctx_init.replace("_", " ")
+            n_ctx = len(ctx_init.split(" "))
+            prefix_words = ctx_init
+        else:
+            prefix_words = " ".join(["X"] * n_ctx)
+        if tokenized_prompts is None:
+            tokenized_prompts = _reference_tokenize([prefix_words + " " + n + "." for n in names])
+        tokens = torch.as_tensor(tokenized_prompts).long().cpu()
+        if ctx_init:
+            ctx_vectors = sd_emb[tokens[0, 1:1 + n_ctx]].clone()
+        else:
+            ctx_vectors = torch.empty(n_ctx, sd_emb.shape[1])
+            nn.init.normal_(ctx_vectors, std=0.02)
+        self.use_focal_loss = bool(_get(T, "USE_FOCAL_LOSS", False))
+        vis_dim = clip_model.state_dict()["text_projection"].shape[1]           # = visual.output_dim (:115)
+        kw = dict(prec_cfg=T.PREC, n_ctx_text=n_ctx, n_ctx_vision=0, depth_text=1, depth_vision=0,
+                  per_image_text=True, meta_hidden=vis_dim // 16, zero_shot_branch=False)
+        if self.use_focal_loss:
+            kw["focal_alpha"] = _focal_alpha_from_cfg(cfg, len(classnames))
+        self._build(cfg, clip_model, tokens, kw, ctx_vectors, device=device)
+
+    def _make_prompt_learner(self, scfg, ctx_init, prefix, suffix, tokens):
+        return _CoCoOpPromptLearner(ctx_init.float(), scfg.arch.embed_dim, prefix, suffix, tokens)
+
+    def _named_for_step(self, scfg):
+        m = self.prompt_learner.meta_net
+        return [("ctx", self.prompt_learner.ctx), ("meta.w1", m.linear1.weight), ("meta.b1", m.linear1.bias),
+                ("meta.w2", m.linear2.weight), ("meta.b2", m.linear2.bias)]
+
+    def forward(self, image, label=None):
+        if self._is_inference(label):
+            return self._eval_logits(image)
+        logits = self._bridged(image.float())[0]
+        if label is None:
+            return logits                                                       # cocoop.py:257-260
+        st = self._step
+        return F.cross_entropy(logits, label) if st.focal_alpha is None else _focal(logits, label, st)
 
 
 # ------------------------------------------------------------------ trainers
@@ -660,6 +838,58 @@ class CoOp(_PromptTrainer):
                 st.compute_logits()                                          # image features are prompt-independent here
                 pred = st.logits.argmax(1)
                 loss_summary["acc"] = float((pred == st.labels.long()).float().mean().item() * 100.0)
+        if (self.batch_idx + 1) == self.num_batches:
+            self.update_lr()
+        return loss_summary
+
+
+@TRAINER_REGISTRY.register(force=True)
+class MaPLe(_PromptTrainer):
+    """Drop-in for trainers/maple.py:257-357."""
+    MODEL_NAME = "MultiModalPromptLearner"
+
+    def check_cfg(self, cfg):
+        assert cfg.TRAINER.MAPLE.PREC in ["fp16", "fp32", "amp"]
+
+    def build_model(self):
+        cfg = self.cfg
+        classnames = self.dm.dataset.classnames
+        clip_model = _load_clip(cfg, "MaPLe")
+        clip_model.float()
+        self.model = MaPLeCustomCLIP(cfg, classnames, clip_model, tokenized_prompts=self._tokens(classnames),
+                                     device=self.device)
+        self._finish_build(self.model)                                       # maple.py:301 registers the whole model
+
+    def forward_backward(self, batch):
+        image, label = self.parse_batch_train(batch)
+        losses = self.model.train_step_fused(image, label, self.optim)
+        loss_summary = {"loss": float(losses.sum().item())}                  # maple.py:325
+        if (self.batch_idx + 1) == self.num_batches:
+            self.update_lr()
+        return loss_summary
+
+
+@TRAINER_REGISTRY.register(force=True)
+class CoCoOp(_PromptTrainer):
+    """Drop-in for trainers/cocoop.py:262-372."""
+    MODEL_NAME = "prompt_learner"
+
+    def check_cfg(self, cfg):
+        assert cfg.TRAINER.COCOOP.PREC in ["fp16", "fp32", "amp"]
+
+    def build_model(self):
+        cfg = self.cfg
+        classnames = self.dm.dataset.classnames
+        clip_model = _load_clip(cfg, "CoCoOp")
+        clip_model.float()
+        self.model = CoCoOpCustomCLIP(cfg, classnames, clip_model, tokenized_prompts=self._tokens(classnames),
+                                      device=self.device)
+        self._finish_build(self.model.prompt_learner)                        # cocoop.py:304
+
+    def forward_backward(self, batch):
+        image, label = self.parse_batch_train(batch)
+        losses = self.model.train_step_fused(image, label, self.optim)
+        loss_summary = {"loss": float(losses.sum().item())}                  # cocoop.py:328
         if (self.batch_idx + 1) == self.num_batches:
             self.update_lr()
         return loss_summary

@@ -329,6 +329,9 @@ def trainer_cfg(trainer="PromptSRC", batch=3, test_batch=5, max_epoch=4, depth=3
                           "IMAGE_LOSS_WEIGHT": 10, "GPA_MEAN": 2, "GPA_STD": 1, "LOSS_TYPE": "ce"},
             "COOP": {"N_CTX": 4, "CSC": False, "CTX_INIT": "", "PREC": prec, "CLASS_TOKEN_POSITION": "end",
                      "LOSS_TYPE": "ce"},
+            "MAPLE": {"N_CTX": 2, "CTX_INIT": "a photo of a", "PREC": prec, "PROMPT_DEPTH": depth,
+                      "USE_FOCAL_LOSS": False},
+            "COCOOP": {"N_CTX": 4, "CTX_INIT": "a photo of a", "PREC": prec, "USE_FOCAL_LOSS": False},
             "B200": {"CUDA_GRAPH": True},
         },
     })

@@ -94,3 +94,45 @@ def test_trainer_dropin_builds_with_reference_names(monkeypatch):
     # CoOp registers only the prompt learner (coop.py:431)
     tr2, _, _ = TC.make_trainer("CoOp", "fp32", device="cpu")
     assert tr2.get_model_names() == ["prompt_learner"] and list(tr2.model._step.params) == ["ctx"]
+
+
+def test_maple_cocoop_dropins_build_with_reference_names(monkeypatch):
+    """MaPLe / CoCoOp host logic with faked kernels: registration names, reference parameter names bound to the flat
+    buffer in its order, launch sequence of one fused step."""
+    fk = FakeKernels()
+    fk.install(monkeypatch)
+    import trainer_checks as TC
+    from psrc_b200 import trainers as T
+    assert {"PromptSRC", "CoOp", "MaPLe", "CoCoOp"} <= set(T.TRAINER_REGISTRY.registered_names())
+    tr, cfg, tokens = TC.make_trainer("MaPLe", "fp32", device="cpu")
+    assert tr.get_model_names() == ["MultiModalPromptLearner"]
+    st = tr.model._step
+    names = {n for n, p in tr.model.named_parameters() if p.requires_grad}
+    want = {"prompt_learner.ctx", "prompt_learner.proj.weight", "prompt_learner.proj.bias"}
+    for i in range(TC.DEPTH - 1):
+        want |= {f"prompt_learner.compound_prompts_text.{i}", f"prompt_learner.compound_prompt_projections.{i}.weight",
+                 f"prompt_learner.compound_prompt_projections.{i}.bias"}
+    assert names == want, names ^ want
+    pl = tr.model.prompt_learner
+    assert pl.proj.weight.data_ptr() == st.params["couple.w.0"].data_ptr() == st.couple_w.data_ptr()
+    assert pl.compound_prompts_text[0].data_ptr() == st.params["text.1"].data_ptr() == st.couple_x[1].data_ptr()
+    assert pl.ctx.data_ptr() == st.couple_x.data_ptr()
+    n0 = len(fk.calls)
+    st.forward_backward()
+    calls = fk.calls[n0:]
+    assert calls.count("small_linear_fwd") == 1 and calls.count("small_linear_bwd") == 1   # all coupling Linears batched
+    assert calls.count("attn_fwd") == 6 and calls.count("attn_bwd") == 6                   # two towers x 3 layers
+    # CoCoOp: one text pass per image -> B x C sequences in ONE tower launch sequence
+    tr2, _, tokens2 = TC.make_trainer("CoCoOp", "fp32", device="cpu")
+    assert tr2.get_model_names() == ["prompt_learner"]
+    st2 = tr2.model._step
+    assert list(st2.params) == ["ctx", "meta.w1", "meta.b1", "meta.w2", "meta.b2"]
+    assert st2.tt.n_seq == TC.B * tokens2.shape[0] and st2.eot.shape == (TC.B * tokens2.shape[0],)
+    assert tr2.model.prompt_learner.meta_net.linear2.weight.data_ptr() == st2.params["meta.w2"].data_ptr()
+    n0 = len(fk.calls)
+    st2.forward_backward()
+    calls = fk.calls[n0:]
+    assert calls.count("small_linear_fwd") == 2 and calls.count("small_linear_bwd") == 2   # meta-net
+    assert calls.count("attn_fwd") == 6 and calls.count("attn_bwd") == 3                   # vision fwd only, text fwd+bwd
+    assert calls.count("prompt_grad") == TC.B and calls.count("ctx_bias_grad") == 1
+    assert calls.count("group_logits_fwd") == 1 and calls.count("group_logits_bwd") == 1

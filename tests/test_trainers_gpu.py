@@ -51,3 +51,31 @@ def test_trainer_bf16_mode_runs():
     m = TC.check_promptsrc_trainer("fp16")          # cfg PREC fp16 -> 16-bit tensor-core mode
     assert max(m["loss_abs_0"], m["loss_abs_1"], m["loss_abs_2"]) < 5e-2, m
     assert m["update_cos"] > 0.99, m
+
+
+@pytest.mark.parametrize("focal", [False, True])
+def test_maple_trainer_steps_and_eval(focal):
+    _need_gpu()
+    m = TC.check_maple("fp32", focal)
+    assert max(m["loss_abs_0"], m["loss_abs_1"], m["loss_abs_2"]) < 5e-5, m
+    assert m["param_after3_maxabs"] < 2e-6 and m["graph_captured"], m
+    assert m["registered"] == ["MultiModalPromptLearner"] and not m["missing_state_keys"], m
+    assert m["n_trainable"] == 1 + 2 + 3 * (TC.DEPTH - 1), m      # ctx, proj.{w,b}, per deeper layer: text + Linear
+    assert m["eval_logits_maxabs"] < 1e-4 and m["eval_argmax_equal"], m
+
+
+@pytest.mark.parametrize("focal", [False, True])
+def test_cocoop_trainer_steps_and_eval(focal):
+    _need_gpu()
+    m = TC.check_cocoop("fp32", focal)
+    assert max(m["loss_abs_0"], m["loss_abs_1"], m["loss_abs_2"]) < 5e-5, m
+    assert m["param_after3_maxabs"] < 2e-6 and m["graph_captured"], m
+    assert m["registered"] == ["prompt_learner"] and m["n_trainable"] == 5, m
+    assert m["eval_logits_maxabs"] < 1e-4 and m["eval_argmax_equal"] and m["eval_shape_ok"], m
+
+
+def test_maple_cocoop_bf16_mode_runs():
+    _need_gpu()
+    for fn in (TC.check_maple, TC.check_cocoop):
+        m = fn("fp16")
+        assert max(m["loss_abs_0"], m["loss_abs_1"], m["loss_abs_2"]) < 5e-2, m

@@ -178,6 +178,115 @@ def check_eval_and_checkpoint(prec="fp32"):
     return m
 
 
+def _seed_trainer_params(tr, values):
+    """Overwrite the trainer's (randomly initialised) prompt-learner parameters with seeded values."""
+    named = dict(tr.model.prompt_learner.named_parameters())
+    with torch.no_grad():
+        for k, v in values.items():
+            named[k].copy_(v.to(named[k].device))
+
+
+def check_maple(prec="fp32", focal=False):
+    """MaPLe trainer: 3 fused steps (eager, then graph replays) vs 3 oracle iterations with torch SGD; eval logits."""
+    import clip_oracle as O
+    from psrc_b200 import synthetic as S
+    shots = [50, 40, 30, 20, 10, 5, 5, 3, 2, 1]
+    tr, cfg, tokens = make_trainer("MaPLe", prec, **{"TRAINER.MAPLE.USE_FOCAL_LOSS": focal,
+                                                     "DATASET.PER_CLASS_SHOTS": shots})
+    arch, n_ctx = S.ARCHS["tiny"], 2
+    sd = S.make_clip_state_dict(arch, seed=0)
+    mp_ = S.make_maple_params(arch, n_ctx, DEPTH, seed=200)
+    _seed_trainer_params(tr, mp_)
+    image, label = S.synthetic_batch(B, tokens.shape[0], 64, seed=1)
+    P = {k: v.clone().requires_grad_(True) for k, v in mp_.items()}
+    P["ctx"] = sd["token_embedding.weight"][tokens[0, 1:1 + n_ctx]].clone().requires_grad_(True)
+    lr = tr.optim.param_groups[0]["lr"]
+    opt = torch.optim.SGD(list(P.values()), lr=lr, momentum=0.9, weight_decay=5e-4)
+    alpha = torch.tensor(S.focal_alpha(shots, len(shots))) if focal else None
+    nd = DEPTH - 1
+    m, batch = {}, {"img": image.pin_memory(), "label": label.pin_memory()}
+    for s_ in range(3):
+        o = O.maple_step(sd, tokens, image, label, P["ctx"], [P[f"compound_prompts_text.{i}"] for i in range(nd)],
+                         (P["proj.weight"], P["proj.bias"]),
+                         [(P[f"compound_prompt_projections.{i}.weight"], P[f"compound_prompt_projections.{i}.bias"])
+                          for i in range(nd)], n_ctx, arch.vision_heads, arch.transformer_heads, focal_alpha=alpha,
+                         use_focal=focal)
+        opt.zero_grad()
+        o["loss"].backward()
+        opt.step()
+        tr.batch_idx = 0
+        out = tr.forward_backward(batch)
+        m[f"loss_abs_{s_}"] = abs(out["loss"] - float(o["loss"].detach()))
+    named = dict(tr.model.prompt_learner.named_parameters())
+    m["param_after3_maxabs"] = max(float((named[k].detach().cpu() - v.detach()).abs().max()) for k, v in P.items())
+    m["graph_captured"] = getattr(tr.model._step, "_graph", None) is not None
+    m["registered"] = tr.get_model_names()
+    m["n_trainable"] = sum(p.requires_grad for p in tr.model.parameters())
+    keys = set(tr.model.state_dict())
+    m["missing_state_keys"] = sorted({"prompt_learner.ctx", "prompt_learner.proj.weight", "prompt_learner.proj.bias",
+                                      "prompt_learner.compound_prompts_text.0",
+                                      "prompt_learner.compound_prompt_projections.1.weight",
+                                      "prompt_learner.token_prefix", "image_encoder.conv1.weight"} - keys)
+    # eval: logits of the UPDATED prompts through the cached-text path vs the oracle
+    tr.set_model_mode("eval")
+    img7, _ = S.synthetic_batch(7, tokens.shape[0], 64, seed=5)
+    with torch.no_grad():
+        lg = tr.model_inference(img7.cuda()).cpu()
+        o = O.maple_step(sd, tokens, img7, torch.zeros(7, dtype=torch.long), P["ctx"],
+                         [P[f"compound_prompts_text.{i}"] for i in range(nd)], (P["proj.weight"], P["proj.bias"]),
+                         [(P[f"compound_prompt_projections.{i}.weight"], P[f"compound_prompt_projections.{i}.bias"])
+                          for i in range(nd)], n_ctx, arch.vision_heads, arch.transformer_heads)
+    m["eval_logits_maxabs"] = float((lg - o["logits"]).abs().max())
+    m["eval_argmax_equal"] = bool((lg.argmax(1) == o["logits"].argmax(1)).all())
+    return m
+
+
+def check_cocoop(prec="fp32", focal=False):
+    """CoCoOp trainer: 3 fused steps vs 3 oracle iterations; eval logits (per-image text passes, ragged test batch)."""
+    import clip_oracle as O
+    from psrc_b200 import synthetic as S
+    shots = [50, 40, 30, 20, 10, 5, 5, 3, 2, 1]
+    tr, cfg, tokens = make_trainer("CoCoOp", prec, **{"TRAINER.COCOOP.USE_FOCAL_LOSS": focal,
+                                                      "DATASET.PER_CLASS_SHOTS": shots})
+    arch, n_ctx = S.ARCHS["tiny"], 4
+    sd = S.make_clip_state_dict(arch, seed=0)
+    mp_ = S.make_cocoop_params(arch, seed=300)
+    _seed_trainer_params(tr, mp_)
+    image, label = S.synthetic_batch(B, tokens.shape[0], 64, seed=1)
+    P = {k: v.clone().requires_grad_(True) for k, v in mp_.items()}
+    P["ctx"] = sd["token_embedding.weight"][tokens[0, 1:1 + n_ctx]].clone().requires_grad_(True)
+    meta = lambda: tuple(P["meta_net." + k] for k in ("linear1.weight", "linear1.bias", "linear2.weight",  # noqa: E731
+                                                      "linear2.bias"))
+    lr = tr.optim.param_groups[0]["lr"]
+    opt = torch.optim.SGD(list(P.values()), lr=lr, momentum=0.9, weight_decay=5e-4)
+    alpha = torch.tensor(S.focal_alpha(shots, len(shots))) if focal else None
+    m, batch = {}, {"img": image.pin_memory(), "label": label.pin_memory()}
+    for s_ in range(3):
+        o = O.cocoop_step(sd, tokens, image, label, P["ctx"], meta(), n_ctx, arch.vision_heads,
+                          arch.transformer_heads, focal_alpha=alpha, use_focal=focal)
+        opt.zero_grad()
+        o["loss"].backward()
+        opt.step()
+        tr.batch_idx = 0
+        out = tr.forward_backward(batch)
+        m[f"loss_abs_{s_}"] = abs(out["loss"] - float(o["loss"].detach()))
+    named = dict(tr.model.prompt_learner.named_parameters())
+    m["param_after3_maxabs"] = max(float((named[k].detach().cpu() - v.detach()).abs().max()) for k, v in P.items())
+    m["graph_captured"] = getattr(tr.model._step, "_graph", None) is not None
+    m["registered"] = tr.get_model_names()
+    m["n_trainable"] = sum(p.requires_grad for p in tr.model.parameters())
+    tr.set_model_mode("eval")
+    img7, _ = S.synthetic_batch(7, tokens.shape[0], 64, seed=5)     # 7 = two chunks of the train batch (3) + a ragged 1
+    with torch.no_grad():
+        lg = tr.model_inference(img7.cuda()).cpu()
+        o = O.cocoop_step(sd, tokens, img7, torch.zeros(7, dtype=torch.long), P["ctx"], meta(), n_ctx,
+                          arch.vision_heads, arch.transformer_heads)
+    m["eval_logits_maxabs"] = float((lg - o["logits"]).abs().max())
+    m["eval_argmax_equal"] = bool((lg.argmax(1) == o["logits"].argmax(1)).all())
+    m["eval_shape_ok"] = tuple(lg.shape) == (7, tokens.shape[0])
+    return m
+
+
 def check_coop(prec="fp32", loss_type="ce"):
     import clip_oracle as O
     from psrc_b200 import synthetic as S
@@ -211,3 +320,7 @@ if __name__ == "__main__":
         for fn in (check_promptsrc_trainer, check_bridge, check_eval_and_checkpoint, check_coop):
             print(f"== {fn.__name__} [{prec}]", fn(prec))
     print("== check_coop focal [fp32]", check_coop("fp32", "focal"))
+    for prec in ("fp32", "fp16"):
+        for focal in (False, True):
+            print(f"== check_maple focal={focal} [{prec}]", check_maple(prec, focal))
+            print(f"== check_cocoop focal={focal} [{prec}]", check_cocoop(prec, focal))
