@@ -16,6 +16,10 @@ int attn_fwd_small(const void* qkv, void* out, float* lse, int act_dtype, int n_
                    cudaStream_t s);
 int attn_bwd_small(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int act_dtype,
                    int grad_dtype, int n_seq, int L, int H, int causal, cudaStream_t s);
+bool attn_small_mma_supported(int L);
+int attn_fwd_small_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s);
+int attn_bwd_small_mma(const void* qkv, const void* dout, const float* lse, void* dqkv, int n_seq, int L, int H,
+                       int causal, cudaStream_t s);
 int attn_fwd_tc(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s);
 int attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int n_seq,
                 int L, int H, int causal, cudaStream_t s);
@@ -24,22 +28,33 @@ int attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float*
 using namespace psrc;
 
 static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+// bf16 fast mode: tcgen05 for 32 < L <= 256, one-warp mma.sync tile for L <= 16, CUDA-core half-warp kernel for
+// L <= 32, flash-style mma.sync otherwise
+static int auto_backend(int L) {
+  if (attn_tc_supported(L)) return 3;
+  if (attn_small_mma_supported(L)) return 5;
+  return attn_small_supported(L) ? 4 : 2;
+}
 
 extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, int n_seq, int L, int H,
                              int causal, int backend, psrc_stream_t stream) {
   PSRC_CHECK_ARG(qkv && out && lse, "psrc_attn_fwd: null pointer");
   PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && H > 0, "psrc_attn_fwd: bad shape n_seq=%d L=%d H=%d", n_seq, L, H);
   PSRC_CHECK_ARG(dtype == PSRC_F32 || dtype == PSRC_BF16, "psrc_attn_fwd: bad dtype");
-  PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_fwd: n_seq=%d exceeds the grid limit 65535", n_seq);
   if (n_seq == 0) return PSRC_OK;
   if (backend == 0)
-    backend = (dtype == PSRC_BF16 && al16(qkv) && al16(out)) ? (attn_tc_supported(L) ? 3 : (attn_small_supported(L) ? 4 : 2))
-                                                             : 1;
+    backend = (dtype == PSRC_BF16 && al16(qkv) && al16(out)) ? auto_backend(L) : 1;
+  if (backend == 5) {
+    PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out) && attn_small_mma_supported(L),
+                   "psrc_attn_fwd: one-tile mma backend needs aligned bf16 and L <= 16 (L=%d)", L);
+    return attn_fwd_small_mma(qkv, out, lse, n_seq, L, H, causal, as_stream(stream));
+  }
   if (backend == 4) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out) && attn_small_supported(L),
                    "psrc_attn_fwd: short-sequence backend needs aligned bf16 and L <= 32 (L=%d)", L);
     return attn_fwd_small(qkv, out, lse, dtype, n_seq, L, H, causal, as_stream(stream));
   }
+  PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_fwd: n_seq=%d exceeds the grid limit 65535 of this backend", n_seq);
   if (backend == 2 || backend == 3) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out), "psrc_attn_fwd: tensor-core backend needs aligned bf16");
     if (backend == 3) {
@@ -56,16 +71,21 @@ extern "C" int psrc_attn_bwd(const void* qkv, const void* out, const void* dout,
   PSRC_CHECK_ARG(qkv && out && dout && lse && dqkv, "psrc_attn_bwd: null pointer");
   PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && H > 0, "psrc_attn_bwd: bad shape n_seq=%d L=%d H=%d", n_seq, L, H);
   PSRC_CHECK_ARG(dtype == PSRC_F32 || dtype == PSRC_BF16, "psrc_attn_bwd: bad dtype");
-  PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_bwd: n_seq=%d exceeds the grid limit 65535", n_seq);
   if (n_seq == 0) return PSRC_OK;
   const bool ok16 = al16(qkv) && al16(out) && al16(dout) && al16(dqkv);
   if (backend == 0)
-    backend = (dtype == PSRC_BF16 && ok16) ? (attn_tc_supported(L) ? 3 : (attn_small_supported(L) ? 4 : 2)) : 1;
+    backend = (dtype == PSRC_BF16 && ok16) ? auto_backend(L) : 1;
+  if (backend == 5) {
+    PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16 && attn_small_mma_supported(L),
+                   "psrc_attn_bwd: one-tile mma backend needs aligned bf16 and L <= 16 (L=%d)", L);
+    return attn_bwd_small_mma(qkv, dout, lse, dqkv, n_seq, L, H, causal, as_stream(stream));
+  }
   if (backend == 4) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16 && attn_small_supported(L),
                    "psrc_attn_bwd: short-sequence backend needs aligned bf16 and L <= 32 (L=%d)", L);
     return attn_bwd_small(qkv, out, dout, lse, dqkv, dtype, dtype, n_seq, L, H, causal, as_stream(stream));
   }
+  PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_bwd: n_seq=%d exceeds the grid limit 65535 of this backend", n_seq);
   if (backend == 2 || backend == 3) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16, "psrc_attn_bwd: tensor-core backend needs aligned bf16");
     if (backend == 3) {

@@ -1,0 +1,293 @@
+// Tensor-core attention for very short sequences (L <= 16, head_dim 64, bf16): the truncated text tower
+// (SURVEY F12).  One warp owns one (sequence, head) problem padded to a single 16 x 16 score tile:
+//   forward : S = Q K^T (8 mma.m16n8k16), softmax in the accumulator fragments, O = P V (8 mma)
+//   backward: S, dP = dO V^T, dS = P o (dP - delta) with delta_i = sum_j P_ij dP_ij (= <dO_i, O_i>, so O is never
+//             read), dQ = dS K, dK = dS^T Q, dV = P^T dO -- 40 mma; P / dS cross to the transposed operand through a
+//             512-byte shared tile and ldmatrix.trans.
+// Q/K/V/dO tiles are staged with coalesced 16-byte loads into padded shared memory (row stride 144 B: conflict-free
+// ldmatrix), results leave through the same tiles with 16-byte stores.  The kernel is HBM-bound: 8 KB (fwd 6 KB) in
+// flight per warp.  Reference: nn.MultiheadAttention core called from PromptSRC/clip/model.py:183/227/285 with the
+// causal mask of model.py:592-598.
+#include "common.cuh"
+
+namespace psrc {
+namespace asm2 {
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr int kLd = 72;    // tile row stride in elements (64 + 8 pad)
+constexpr int kXLd = 24;   // P / dS tile row stride (16 + 8 pad)
+constexpr int kWarps = 4;
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ void ldsm4(uint32_t (&r)[4], const __nv_bfloat16* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(smem_u32(p)));
+}
+__device__ __forceinline__ void ldsm4t(uint32_t (&r)[4], const __nv_bfloat16* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(smem_u32(p)));
+}
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// stage L rows of 64 bf16 (row stride `ld` elements in global) into a [16][kLd] tile, zero-filling rows >= L
+__device__ __forceinline__ void stage_tile(__nv_bfloat16* tile, const __nv_bfloat16* __restrict__ src, long long ld,
+                                           int L, int lane) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int idx = lane + 32 * i, r = idx >> 3, c = idx & 7;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (r < L) v = __ldg(reinterpret_cast<const uint4*>(src + (long long)r * ld) + c);
+    *reinterpret_cast<uint4*>(tile + r * kLd + c * 8) = v;
+  }
+}
+// the inverse: rows < L of a [16][kLd] tile to global with 16-byte stores
+__device__ __forceinline__ void unstage_tile(const __nv_bfloat16* tile, __nv_bfloat16* __restrict__ dst, long long ld,
+                                             int L, int lane) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int idx = lane + 32 * i, r = idx >> 3, c = idx & 7;
+    if (r < L) *(reinterpret_cast<uint4*>(dst + (long long)r * ld) + c) =
+        *reinterpret_cast<const uint4*>(tile + r * kLd + c * 8);
+  }
+}
+// accumulator fragments of a [16 x 64] result (8 n-tiles) -> bf16 tile, scaled
+__device__ __forceinline__ void frags_to_tile(__nv_bfloat16* tile, const float (&c)[8][4], float s0, float s1,
+                                              int g, int t) {
+#pragma unroll
+  for (int n = 0; n < 8; ++n) {
+    *reinterpret_cast<uint32_t*>(tile + g * kLd + n * 8 + 2 * t) = pack_bf16(c[n][0] * s0, c[n][1] * s0);
+    *reinterpret_cast<uint32_t*>(tile + (g + 8) * kLd + n * 8 + 2 * t) = pack_bf16(c[n][2] * s1, c[n][3] * s1);
+  }
+}
+
+// C[16 x 16] = A[16 x 64] . B[16 x 64]^T, both tiles row-major [row][64]  (Q K^T, dO V^T)
+__device__ __forceinline__ void mma_abt(float (&c)[2][4], const __nv_bfloat16* A, const __nv_bfloat16* B, int lane) {
+  const int arow = (lane & 7) + ((lane >> 3) & 1) * 8, acol = (lane >> 4) * 8;
+  const int brow = lane & 7, bcol = (lane >> 3) * 8;
+#pragma unroll
+  for (int n = 0; n < 2; ++n)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c[n][i] = 0.f;
+#pragma unroll
+  for (int kk = 0; kk < 4; kk += 2) {
+    uint32_t a0[4], a1[4], b[2][4];
+    ldsm4(a0, A + arow * kLd + kk * 16 + acol);
+    ldsm4(a1, A + arow * kLd + (kk + 1) * 16 + acol);
+    ldsm4(b[0], B + brow * kLd + kk * 16 + bcol);          // n-tile 0, k-steps kk, kk+1
+    ldsm4(b[1], B + (8 + brow) * kLd + kk * 16 + bcol);    // n-tile 1
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+      mma16816(c[n], a0, b[n][0], b[n][1]);
+      mma16816(c[n], a1, b[n][2], b[n][3]);
+    }
+  }
+}
+// C[16 x 64] = A[16 x 16] . B[16 x 64], A given as a register fragment, B tile row-major [k][64]  (P V, dS K, ...)
+__device__ __forceinline__ void mma_ab(float (&c)[8][4], const uint32_t (&a)[4], const __nv_bfloat16* B, int lane) {
+  const int brow = (lane & 7) + ((lane >> 3) & 1) * 8, bcol = (lane >> 4) * 8;
+#pragma unroll
+  for (int n = 0; n < 8; n += 2) {
+    uint32_t b[4];
+    ldsm4t(b, B + brow * kLd + n * 8 + bcol);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c[n][i] = c[n + 1][i] = 0.f;
+    mma16816(c[n], a, b[0], b[1]);
+    mma16816(c[n + 1], a, b[2], b[3]);
+  }
+}
+
+template <bool kCausal>
+__global__ void __launch_bounds__(kWarps * 32)
+attn_small_mma_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
+                          float* __restrict__ lse, int n_prob, int L, int H) {
+  __shared__ __align__(16) __nv_bfloat16 sm[kWarps][3][16 * kLd];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int pr = blockIdx.x * kWarps + warp;
+  if (pr >= n_prob) return;
+  const int seq = pr / H, h = pr % H, D = H * 64;
+  const long long ld = 3LL * D;
+  const __nv_bfloat16* base = qkv + (long long)seq * L * ld + h * 64;
+  __nv_bfloat16 *Qs = sm[warp][0], *Ks = sm[warp][1], *Vs = sm[warp][2];
+  stage_tile(Qs, base, ld, L, lane);
+  stage_tile(Ks, base + D, ld, L, lane);
+  stage_tile(Vs, base + 2 * D, ld, L, lane);
+  __syncwarp();
+  const int g = lane >> 2, t = lane & 3;
+  float s[2][4];
+  mma_abt(s, Qs, Ks, lane);
+  // scores -> log2 domain, mask (key >= L, causal key > query)
+  float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+  for (int n = 0; n < 2; ++n)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int row = g + (i >> 1) * 8, col = n * 8 + 2 * t + (i & 1);
+      const bool ok = col < L && (!kCausal || col <= row);
+      s[n][i] = ok ? s[n][i] * (0.125f * kLog2e) : -INFINITY;
+      if (i < 2) m0 = fmaxf(m0, s[n][i]); else m1 = fmaxf(m1, s[n][i]);
+    }
+  m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1));
+  m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+  m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1));
+  m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+  float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+  for (int n = 0; n < 2; ++n)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      s[n][i] = ex2(s[n][i] - ((i < 2) ? m0 : m1));      // exp2(-inf) = 0 for masked entries
+      if (i < 2) sum0 += s[n][i]; else sum1 += s[n][i];
+    }
+  sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1);
+  sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+  sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1);
+  sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+  uint32_t p[4] = {pack_bf16(s[0][0], s[0][1]), pack_bf16(s[0][2], s[0][3]), pack_bf16(s[1][0], s[1][1]),
+                   pack_bf16(s[1][2], s[1][3])};
+  float o[8][4];
+  mma_ab(o, p, Vs, lane);
+  __syncwarp();                       // every lane is done reading Qs (mma_abt) before it is reused for O
+  frags_to_tile(Qs, o, 1.f / sum0, 1.f / sum1, g, t);
+  __syncwarp();
+  unstage_tile(Qs, out + (long long)seq * L * D + h * 64, (long long)D, L, lane);
+  if (t == 0) {
+    float* l = lse + ((long long)seq * H + h) * L;
+    if (g < L) l[g] = (m0 + log2f(sum0)) * kLn2;
+    if (g + 8 < L) l[g + 8] = (m1 + log2f(sum1)) * kLn2;
+  }
+}
+
+struct BwdSmem {
+  __nv_bfloat16 q[16 * kLd], k[16 * kLd], v[16 * kLd], d[16 * kLd];
+  __nv_bfloat16 p[16 * kXLd], ds[16 * kXLd];
+};
+
+template <bool kCausal>
+__global__ void __launch_bounds__(kWarps * 32)
+attn_small_mma_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
+                          const float* __restrict__ lse, __nv_bfloat16* __restrict__ dqkv, int n_prob, int L, int H) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int pr = blockIdx.x * kWarps + warp;
+  if (pr >= n_prob) return;
+  BwdSmem& S = reinterpret_cast<BwdSmem*>(smem_raw)[warp];
+  const int seq = pr / H, h = pr % H, D = H * 64;
+  const long long ld = 3LL * D;
+  const __nv_bfloat16* base = qkv + (long long)seq * L * ld + h * 64;
+  stage_tile(S.q, base, ld, L, lane);
+  stage_tile(S.k, base + D, ld, L, lane);
+  stage_tile(S.v, base + 2 * D, ld, L, lane);
+  stage_tile(S.d, dout + (long long)seq * L * D + h * 64, (long long)D, L, lane);
+  const int g = lane >> 2, t = lane & 3;
+  const float* lrow = lse + ((long long)seq * H + h) * L;
+  const float l0 = (g < L) ? lrow[g] * kLog2e : 0.f, l1 = (g + 8 < L) ? lrow[g + 8] * kLog2e : 0.f;
+  __syncwarp();
+  float s[2][4], dp[2][4];
+  mma_abt(s, S.q, S.k, lane);
+  mma_abt(dp, S.d, S.v, lane);
+  float del0 = 0.f, del1 = 0.f;
+#pragma unroll
+  for (int n = 0; n < 2; ++n)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int row = g + (i >> 1) * 8, col = n * 8 + 2 * t + (i & 1);
+      const bool ok = row < L && col < L && (!kCausal || col <= row);
+      s[n][i] = ok ? ex2(s[n][i] * (0.125f * kLog2e) - ((i < 2) ? l0 : l1)) : 0.f;   // P_ij
+      if (i < 2) del0 = fmaf(s[n][i], dp[n][i], del0); else del1 = fmaf(s[n][i], dp[n][i], del1);
+    }
+  del0 += __shfl_xor_sync(0xffffffffu, del0, 1);
+  del0 += __shfl_xor_sync(0xffffffffu, del0, 2);
+  del1 += __shfl_xor_sync(0xffffffffu, del1, 1);
+  del1 += __shfl_xor_sync(0xffffffffu, del1, 2);
+  uint32_t dsf[4];
+#pragma unroll
+  for (int n = 0; n < 2; ++n) {
+    const float d0 = s[n][0] * (dp[n][0] - del0), d1 = s[n][1] * (dp[n][1] - del0);
+    const float d2 = s[n][2] * (dp[n][2] - del1), d3 = s[n][3] * (dp[n][3] - del1);
+    dsf[2 * n] = pack_bf16(d0, d1);
+    dsf[2 * n + 1] = pack_bf16(d2, d3);
+    *reinterpret_cast<uint32_t*>(S.ds + g * kXLd + n * 8 + 2 * t) = dsf[2 * n];
+    *reinterpret_cast<uint32_t*>(S.ds + (g + 8) * kXLd + n * 8 + 2 * t) = dsf[2 * n + 1];
+    *reinterpret_cast<uint32_t*>(S.p + g * kXLd + n * 8 + 2 * t) = pack_bf16(s[n][0], s[n][1]);
+    *reinterpret_cast<uint32_t*>(S.p + (g + 8) * kXLd + n * 8 + 2 * t) = pack_bf16(s[n][2], s[n][3]);
+  }
+  __syncwarp();
+  // transposed operand fragments: A = X^T with X[q][k] row-major
+  uint32_t dst_[4], pt_[4];
+  {
+    const int xr = (lane & 7) + (lane >> 4) * 8, xc = ((lane >> 3) & 1) * 8;
+    ldsm4t(dst_, S.ds + xr * kXLd + xc);
+    ldsm4t(pt_, S.p + xr * kXLd + xc);
+  }
+  float acc[8][4];
+  __nv_bfloat16* drow = dqkv + (long long)seq * L * ld + h * 64;
+  // dV = P^T dO  (reads S.d), staged out through S.v (V is no longer needed)
+  mma_ab(acc, pt_, S.d, lane);
+  frags_to_tile(S.v, acc, 1.f, 1.f, g, t);
+  // dQ = 0.125 dS K  (reads S.k), staged out through S.d (every lane has finished reading S.d only after a sync)
+  mma_ab(acc, dsf, S.k, lane);
+  __syncwarp();
+  frags_to_tile(S.d, acc, 0.125f, 0.125f, g, t);
+  // dK = 0.125 dS^T Q  (reads S.q), staged out through S.k
+  mma_ab(acc, dst_, S.q, lane);
+  __syncwarp();
+  frags_to_tile(S.k, acc, 0.125f, 0.125f, g, t);
+  __syncwarp();
+  unstage_tile(S.d, drow, ld, L, lane);
+  unstage_tile(S.k, drow + D, ld, L, lane);
+  unstage_tile(S.v, drow + 2 * D, ld, L, lane);
+}
+
+}  // namespace asm2
+
+bool attn_small_mma_supported(int L) { return L >= 1 && L <= 16; }
+
+int attn_fwd_small_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s) {
+  using namespace asm2;
+  const int n_prob = n_seq * H;
+  const int grid = (n_prob + kWarps - 1) / kWarps;
+  const __nv_bfloat16* q = reinterpret_cast<const __nv_bfloat16*>(qkv);
+  __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+  if (causal) attn_small_mma_fwd_kernel<true><<<grid, kWarps * 32, 0, s>>>(q, o, lse, n_prob, L, H);
+  else attn_small_mma_fwd_kernel<false><<<grid, kWarps * 32, 0, s>>>(q, o, lse, n_prob, L, H);
+  PSRC_CHECK_LAUNCH();
+  return PSRC_OK;
+}
+
+int attn_bwd_small_mma(const void* qkv, const void* dout, const float* lse, void* dqkv, int n_seq, int L, int H,
+                       int causal, cudaStream_t s) {
+  using namespace asm2;
+  const int n_prob = n_seq * H;
+  const int grid = (n_prob + kWarps - 1) / kWarps;
+  const int bytes = kWarps * (int)sizeof(BwdSmem);
+  static bool attr_set = false;
+  if (!attr_set) {
+    PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    attr_set = true;
+  }
+  const __nv_bfloat16* q = reinterpret_cast<const __nv_bfloat16*>(qkv);
+  const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(dout);
+  __nv_bfloat16* dq = reinterpret_cast<__nv_bfloat16*>(dqkv);
+  if (causal) attn_small_mma_bwd_kernel<true><<<grid, kWarps * 32, bytes, s>>>(q, d, lse, dq, n_prob, L, H);
+  else attn_small_mma_bwd_kernel<false><<<grid, kWarps * 32, bytes, s>>>(q, d, lse, dq, n_prob, L, H);
+  PSRC_CHECK_LAUNCH();
+  return PSRC_OK;
+}
+
+}  // namespace psrc
