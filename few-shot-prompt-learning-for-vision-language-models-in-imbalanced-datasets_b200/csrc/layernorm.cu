@@ -132,8 +132,15 @@ ln_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x, const int32
   const float mean = mean_in[s], rstd = rstd_in[s];
   const float* xr = x + (long long)r * D;
   const T* dyr = dy + (long long)s * D;
-  float4 xh[NV], gd[NV];
+  float4 xh[NV], gd[NV], res[NV];
   float s1 = 0.f, s2 = 0.f;
+  // the residual-gradient row is fetched up front with the other operands: dx_out may alias dx_in, so a load placed
+  // after the first store below could not be hoisted by the compiler and every slot would pay a full DRAM round trip
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    int c = (lane + 32 * i) * 4;
+    res[i] = (dx_in && c < D) ? load4<float>(dx_in + (long long)r * D + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     int c = (lane + 32 * i) * 4;
@@ -158,10 +165,7 @@ ln_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x, const int32
       o.y = rstd * (gd[i].y - s1 - xh[i].y * s2);
       o.z = rstd * (gd[i].z - s1 - xh[i].z * s2);
       o.w = rstd * (gd[i].w - s1 - xh[i].w * s2);
-      if (dx_in) {
-        float4 p = load4<float>(dx_in + (long long)r * D + c);
-        o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
-      }
+      o.x += res[i].x; o.y += res[i].y; o.z += res[i].z; o.w += res[i].w;
       store4<float>(dx_out + (long long)r * D + c, o);
       if (dx_act) store4<TA>(dx_act + (long long)r * D + c, o);
     }

@@ -329,17 +329,19 @@ class PromptedClipStep:
         return self.logits
 
     # ------------------------------------------------------------------ full step
-    def forward_train(self):
-        """Forward of CustomCLIP.forward in training mode (promptsrc.py:183-201; coop.py:351-365): text features,
-        image features, logits and -- PromptSRC -- the frozen-teacher features / logits.  No loss, no backward."""
+    def forward_text(self):
+        """The image-independent part of the forward: the text tower over this rank's class prompts (+ all-gather).
+        Runs while the batch is still on its way to the device (`train_step_host`).  CoCoOp's text pass depends on
+        the image features and therefore belongs to `forward_rest`."""
+        if not self.per_image:
+            self.text_features()
+
+    def forward_rest(self):
         cfg = self.cfg
         B, C, E = cfg.batch, cfg.n_cls, self.E
+        self.image_features()
         if self.per_image:                 # the context shift needs the image features first (cocoop.py:241-246)
-            self.image_features()
             self.text_features()
-        else:
-            self.text_features()
-            self.image_features()
         self.compute_logits()
         if cfg.zero_shot_branch:
             self.zero_shot_features()
@@ -347,13 +349,24 @@ class PromptedClipStep:
                                  alpha=self.scale)                          # promptsrc.py:201
         return self.logits
 
+    def forward_train(self):
+        """Forward of CustomCLIP.forward in training mode (promptsrc.py:183-201; coop.py:351-365): text features,
+        image features, logits and -- PromptSRC -- the frozen-teacher features / logits.  No loss, no backward."""
+        self.forward_text()
+        return self.forward_rest()
+
     def forward_backward(self):
         """Inputs: self.image / self.labels (device).  Fills self.losses, self.logits and self.flat_grad
         (all-reduced across ranks).  The optimizer step is the caller's (trainer / bench)."""
+        self.forward_text()
+        return self.backward_after_text()
+
+    def backward_after_text(self):
+        """Everything of the step that needs the image batch: vision towers, logits, losses, prompt-only backward."""
         cfg = self.cfg
         C = cfg.n_cls
         zs = cfg.zero_shot_branch
-        self.forward_train()
+        self.forward_rest()
         multi = cfg.world_size > 1
         d_that_l1 = self.d_that_l1 if self.share_text else self.d_that_l
         ops.loss_fwd_bwd(self.logits, self.labels, self.d_logits, self.losses, self.loss_scratch,
@@ -513,6 +526,14 @@ class PromptedClipStep:
         self.sgd()
         return self.losses
 
+    def _step_part(self, part):
+        """part 0: image-independent prefix (text tower forward); part 1: the rest of the train step."""
+        if part == 0:
+            self.forward_text()
+        else:
+            self.backward_after_text()
+            self.sgd()
+
     def capture(self, warmup: int = 2):
         """Capture train_step into a CUDA graph (shapes are static; every kernel is stateless).  Single
         process only: with world_size > 1 the step stays eager so NCCL runs on its own stream."""
@@ -524,18 +545,25 @@ class PromptedClipStep:
             for _ in range(warmup):
                 self.train_step()
         torch.cuda.current_stream().wait_stream(s)
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            self.train_step()
+        # two graphs: the text-tower prefix does not read the image batch, so `train_step_host` replays it while the
+        # host->device copy of the batch is still in flight on the copy stream
+        g0, g1 = (None if self.per_image else torch.cuda.CUDAGraph()), torch.cuda.CUDAGraph()
+        if g0 is not None:
+            with torch.cuda.graph(g0):
+                self._step_part(0)
+        with torch.cuda.graph(g1):
+            self._step_part(1)
         self.flat_param.copy_(keep[0])
         self.mom_buf.copy_(keep[1])
-        self._graph = g
-        return g
+        self._graph = (g0, g1)
+        return self._graph
 
     def run(self):
         """One train step on the resident inputs: graph replay when captured, eager otherwise."""
         if getattr(self, "_graph", None) is not None:
-            self._graph.replay()
+            if self._graph[0] is not None:
+                self._graph[0].replay()
+            self._graph[1].replay()
         else:
             self.train_step()
         return self.losses
@@ -543,10 +571,33 @@ class PromptedClipStep:
     def train_step_host(self, image_host: torch.Tensor, label_host: torch.Tensor) -> float:
         """The call the Dassl trainer makes per batch (PromptSRC.forward_backward, promptsrc.py:285-330):
         host batch in (pinned fp32 [B,3,R,R], int64 [B]) -> H2D -> step -> SGD -> `loss.item()` (D2H sync)."""
-        self.image.copy_(image_host, non_blocking=True)                     # parse_batch_train :384-387
-        self.labels.copy_(label_host.to(torch.int32), non_blocking=True)
-        self.run()
+        self.run_host(image_host, label_host)
         return float(self.losses.cpu().sum())                               # :330 (16-byte D2H)
+
+    def run_host(self, image_host: torch.Tensor, label_host: torch.Tensor):
+        """Batch in from the host (pinned: truly asynchronous) on a copy stream, overlapped with the image-independent
+        text-tower forward on the compute stream; the rest of the step waits for the copy.  Losses stay on the device."""
+        main = torch.cuda.current_stream()
+        cs = getattr(self, "_copy_stream", None)
+        if cs is None:
+            cs = self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._copy_done = torch.cuda.Event()
+        cs.wait_stream(main)                        # the previous step has finished reading self.image / self.labels
+        with torch.cuda.stream(cs):
+            self.image.copy_(image_host, non_blocking=True)                 # parse_batch_train :384-387
+            self.labels.copy_(label_host.to(torch.int32), non_blocking=True)
+            self._copy_done.record(cs)
+        graphs = getattr(self, "_graph", None)
+        if graphs is not None:
+            if graphs[0] is not None:
+                graphs[0].replay()
+            main.wait_event(self._copy_done)
+            graphs[1].replay()
+        else:
+            self._step_part(0)
+            main.wait_event(self._copy_done)
+            self._step_part(1)
+        return self.losses
 
 
 class VisionInference:

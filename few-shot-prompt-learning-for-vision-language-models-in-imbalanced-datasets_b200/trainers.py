@@ -419,12 +419,15 @@ class _CustomCLIPBase(nn.Module):
             raise RuntimeError(f"training batch {image.shape[0]} != configured per-rank batch {st.cfg.batch} "
                                "(Dassl's train loader drops the last short batch, data_manager.py:42)")
         optim.sync_lr()
-        st.image.copy_(image, non_blocking=True)
-        st.labels.copy_(label.to(torch.int32), non_blocking=True)
         if self._use_graph and getattr(st, "_graph", None) is None and self._eager_steps >= 1:
             st.capture(warmup=1)
         self._eager_steps += 1
-        st.run()
+        if image.is_cuda:
+            st.image.copy_(image, non_blocking=True)
+            st.labels.copy_(label.to(torch.int32), non_blocking=True)
+            st.run()
+        else:
+            st.run_host(image, label)        # H2D on the copy stream, under the text-tower forward
         if self._infer is not None:
             self._infer.text_valid = False
         return st.losses
