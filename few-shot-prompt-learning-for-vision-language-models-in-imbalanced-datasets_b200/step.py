@@ -535,9 +535,9 @@ class PromptedClipStep:
             self.sgd()
 
     def capture(self, warmup: int = 2):
-        """Capture train_step into a CUDA graph (shapes are static; every kernel is stateless).  Single
-        process only: with world_size > 1 the step stays eager so NCCL runs on its own stream."""
-        assert self.cfg.world_size == 1, "graph capture is used on the single-GPU path only"
+        """Capture train_step into CUDA graphs (shapes are static; every kernel is stateless).  With world_size > 1
+        the three NCCL collectives of the step are captured with it (every rank must call capture() at the same
+        point, after at least one eager step has initialised the communicator)."""
         keep = (self.flat_param.clone(), self.mom_buf.clone())
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
