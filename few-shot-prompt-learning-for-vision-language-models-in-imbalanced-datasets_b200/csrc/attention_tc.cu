@@ -52,6 +52,36 @@ constexpr uint32_t kIdescBase = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)
 __device__ __forceinline__ uint32_t idesc_kk(int n) { return kIdescBase | ((uint32_t)(n >> 3) << 17); }
 constexpr uint32_t kIdescMn64 = kIdescBase | (1u << 16) | ((uint32_t)(64 >> 3) << 17);  // B MN-major, N = 64
 
+
+// ---- softmax helpers: W columns of one TMEM lane per call, four independent max / sum chains (a single chain of
+//      ~200 dependent FMNMX / FADD is latency-bound with one softmax warp per scheduler), no per-element predicates
+//      unless the chunk straddles the row's valid length
+template <int W, bool MASK>
+__device__ __forceinline__ void chunk_max(const uint32_t (&r)[W], int c0, int ncol, float (&m)[4]) {
+#pragma unroll
+  for (int i = 0; i < W; ++i) {
+    float v = __uint_as_float(r[i]);
+    if (MASK && c0 + i >= ncol) v = -INFINITY;
+    m[i & 3] = fmaxf(m[i & 3], v);
+  }
+}
+template <int W, bool MASK>
+__device__ __forceinline__ void chunk_exp(const uint32_t (&r)[W], uint32_t (&pk)[W / 2], int c0, int ncol,
+                                          float scale_log2, float ms, float (&sum)[4]) {
+#pragma unroll
+  for (int i = 0; i < W / 2; ++i) {
+    float p0 = ex2(fmaf(__uint_as_float(r[2 * i]), scale_log2, -ms));
+    float p1 = ex2(fmaf(__uint_as_float(r[2 * i + 1]), scale_log2, -ms));
+    if (MASK) {
+      if (c0 + 2 * i >= ncol) p0 = 0.f;
+      if (c0 + 2 * i + 1 >= ncol) p1 = 0.f;
+    }
+    sum[(2 * i) & 3] += p0;
+    sum[(2 * i + 1) & 3] += p1;
+    pk[i] = pack2(p0, p1);
+  }
+}
+
 // ------------------------------------------------------------------------------------------- forward
 constexpr int kFwdThreads = 160;  // warps 0-3: softmax + epilogue (one TMEM lane each); warp 4: TMEM/TMA/MMA
 constexpr uint32_t kFwdO = 128;   // TMEM column of the O accumulator (S at 0, P packed over S)
@@ -132,6 +162,57 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
       // columns any lane of this warp needs (warp-uniform loop bound)
       int cmax = Lp;
       if (kCausal) cmax = min(Lp, (t * 128 + warp * 32 + 32 + 15) & ~15);
+      float ms, sum;
+      if (!kCausal) {
+        // ---- fast path (vision tower): every row sees all L keys; only the last chunk straddles L
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        int c0 = 0;
+        for (; c0 + 64 <= Lp; c0 += 64) {          // two loads in flight per wait
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32(tl + c0, r0);
+          tmem_ld_32x32(tl + c0 + 32, r1);
+          tmem_ld_wait();
+          if (c0 + 64 <= L) {
+            chunk_max<32, false>(r0, c0, L, mx);
+            chunk_max<32, false>(r1, c0 + 32, L, mx);
+          } else {
+            chunk_max<32, true>(r0, c0, L, mx);
+            chunk_max<32, true>(r1, c0 + 32, L, mx);
+          }
+        }
+        if (c0 + 32 <= Lp) {
+          uint32_t r0[32];
+          tmem_ld_32x32(tl + c0, r0);
+          tmem_ld_wait();
+          if (c0 + 32 <= L) chunk_max<32, false>(r0, c0, L, mx); else chunk_max<32, true>(r0, c0, L, mx);
+          c0 += 32;
+        }
+        if (c0 < Lp) {
+          uint32_t r0[16];
+          tmem_ld_32x16(tl + c0, r0);
+          tmem_ld_wait();
+          chunk_max<16, true>(r0, c0, L, mx);
+        }
+        ms = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * scale_log2;
+        float sm4[4] = {0.f, 0.f, 0.f, 0.f};
+        c0 = 0;
+        for (; c0 + 32 <= Lp; c0 += 32) {
+          uint32_t r0[32], pk[16];
+          tmem_ld_32x32(tl + c0, r0);
+          tmem_ld_wait();
+          if (c0 + 32 <= L) chunk_exp<32, false>(r0, pk, c0, L, scale_log2, ms, sm4);
+          else chunk_exp<32, true>(r0, pk, c0, L, scale_log2, ms, sm4);
+          tmem_st_32x16(tl + (c0 >> 1), pk);
+        }
+        if (c0 < Lp) {
+          uint32_t r0[16], pk[8];
+          tmem_ld_32x16(tl + c0, r0);
+          tmem_ld_wait();
+          chunk_exp<16, true>(r0, pk, c0, L, scale_log2, ms, sm4);
+          tmem_st_32x8(tl + (c0 >> 1), pk);
+        }
+        sum = (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
+      } else {
       // ---- pass 1: row maximum
       float m = -INFINITY;
       for (int c0 = 0; c0 < cmax; c0 += 32) {
@@ -151,9 +232,9 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
             if (c0 + i < ncol) m = fmaxf(m, __uint_as_float(r[i]));
         }
       }
-      const float ms = m * scale_log2;
+      ms = m * scale_log2;
       // ---- pass 2: P = exp2(S*c - m*c) as packed bf16 over the S columns, row sum in fp32
-      float sum = 0.f;
+      sum = 0.f;
       for (int c0 = 0; c0 < Lp; c0 += 32) {
         if (c0 + 32 <= Lp) {
           uint32_t r[32], pk[16];
@@ -187,6 +268,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
           tmem_st_32x8(tl + (c0 >> 1), pk);
         }
       }
+      }
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -198,6 +280,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
       tmem_ld_32x32(tl + kFwdO, o0);
       tmem_ld_32x32(tl + kFwdO + 32, o1);
       tmem_ld_wait();
+      // O is in registers: hand the TMEM tile back to the MMA warp before the global stores
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_e);
       if (row < L) {
         const float inv = 1.f / sum;
         uint4* dst = reinterpret_cast<uint4*>(out + ((long long)seq * L + row) * D + h * 64);
@@ -221,9 +307,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
         }
         lse[((long long)seq * H + h) * L + row] = (ms + log2f(sum)) * kLn2;
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_e);
     }
   }
   tc_fence_before();
@@ -279,7 +362,7 @@ __device__ __forceinline__ void store_row32(__nv_bfloat16* dst, const uint32_t (
 // One 16*NW-column chunk of the recomputation.  kKeysOnLanes = false: this thread's lane is query `row`,
 // columns are keys; true: lane is key `row`, columns are queries (per-column lse/delta from shared memory).
 // Writes dS (and P when kKeysOnLanes) as packed bf16 over the first half of the consumed fp32 columns.
-template <int NC, bool kKeysOnLanes, bool kCausal>
+template <int NC, bool kKeysOnLanes, bool kCausal, bool kMaskCols>
 __device__ __forceinline__ void bwd_chunk(uint32_t t_s, uint32_t t_dp, uint32_t t_ps, uint32_t t_ds, int c0,
                                           int row, int L, float scale_log2, float lse2_row, float delta_row,
                                           const float* lse2_s, const float* delta_s) {
@@ -291,24 +374,37 @@ __device__ __forceinline__ void bwd_chunk(uint32_t t_s, uint32_t t_dp, uint32_t 
     tmem_ld_32x16(t_s + c0, reinterpret_cast<uint32_t(&)[16]>(s));
     tmem_ld_32x16(t_dp + c0, reinterpret_cast<uint32_t(&)[16]>(dp));
   }
+  // per-column statistics (keys on lanes) as 16-byte shared-memory loads, issued under the TMEM load latency
+  float l2c[kKeysOnLanes ? NC : 1], dlc[kKeysOnLanes ? NC : 1];
+  if (kKeysOnLanes) {
+#pragma unroll
+    for (int i = 0; i < NC; i += 4) {
+      const float4 a = *reinterpret_cast<const float4*>(lse2_s + c0 + i);
+      const float4 b = *reinterpret_cast<const float4*>(delta_s + c0 + i);
+      l2c[i] = a.x; l2c[i + 1] = a.y; l2c[i + 2] = a.z; l2c[i + 3] = a.w;
+      dlc[i] = b.x; dlc[i + 1] = b.y; dlc[i + 2] = b.z; dlc[i + 3] = b.w;
+    }
+  }
   tmem_ld_wait();
   float pv[2], dv[2];
 #pragma unroll
   for (int i = 0; i < NC; ++i) {
     const int col = c0 + i;
-    float l2 = lse2_row, dl = delta_row;
-    bool valid;
-    if (kKeysOnLanes) {
-      l2 = lse2_s[col];
-      dl = delta_s[col];
-      valid = row < L && col < L && (!kCausal || row <= col);
-    } else {
-      valid = col < L && (!kCausal || col <= row);
+    const float l2 = kKeysOnLanes ? l2c[kKeysOnLanes ? i : 0] : lse2_row;
+    const float dl = kKeysOnLanes ? dlc[kKeysOnLanes ? i : 0] : delta_row;
+    // non-causal: padded QUERIES carry lse2 = 1e30 (P = 0) and padded lanes are never stored, so only padded KEY
+    // columns of the queries-on-lanes orientation need a mask, and only in the chunk that straddles L
+    bool valid = true;
+    if (kCausal) {
+      valid = kKeysOnLanes ? (row < L && col < L && row <= col) : (col < L && col <= row);
+    } else if (kMaskCols && !kKeysOnLanes) {
+      valid = col < L;
     }
-    float p = 0.f, d = 0.f;
-    if (valid) {
-      p = ex2(fmaf(__uint_as_float(s[i]), scale_log2, -l2));
-      d = p * (__uint_as_float(dp[i]) - dl);
+    float p = ex2(fmaf(__uint_as_float(s[i]), scale_log2, -l2));
+    float d = p * (__uint_as_float(dp[i]) - dl);
+    if (kCausal || (kMaskCols && !kKeysOnLanes)) {
+      p = valid ? p : 0.f;
+      d = valid ? d : 0.f;
     }
     pv[i & 1] = p;
     dv[i & 1] = d;
@@ -460,16 +556,21 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
       const uint32_t t_ps = tl + kColS + c_lo - (c_lo >> 1), t_ds_q = t_ps, t_ds_k = tl + kColDP + c_lo - (c_lo >> 1);
       const float l2r = lse2_s[row < 256 ? row : 0], dlr = delta_s[row < 256 ? row : 0];
       for (int c0 = c_lo; c0 < c_hi; c0 += 32) {
+        const bool wide = c0 + 32 <= c_hi;
+        const bool straddles = c0 + (wide ? 32 : 16) > L;   // chunk contains padded key columns
         if (qlanes) {
-          if (c0 + 32 <= c_hi)
-            bwd_chunk<32, false, kCausal>(t_s, t_dp, t_ps, t_ds_q, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
-          else
-            bwd_chunk<16, false, kCausal>(t_s, t_dp, t_ps, t_ds_q, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+          if (wide) {
+            if (straddles) bwd_chunk<32, false, kCausal, true>(t_s, t_dp, t_ps, t_ds_q, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+            else bwd_chunk<32, false, kCausal, false>(t_s, t_dp, t_ps, t_ds_q, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+          } else {
+            if (straddles) bwd_chunk<16, false, kCausal, true>(t_s, t_dp, t_ps, t_ds_q, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+            else bwd_chunk<16, false, kCausal, false>(t_s, t_dp, t_ps, t_ds_q, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+          }
         } else {
-          if (c0 + 32 <= c_hi)
-            bwd_chunk<32, true, kCausal>(t_s, t_dp, t_ps, t_ds_k, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+          if (wide)
+            bwd_chunk<32, true, kCausal, false>(t_s, t_dp, t_ps, t_ds_k, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
           else
-            bwd_chunk<16, true, kCausal>(t_s, t_dp, t_ps, t_ds_k, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+            bwd_chunk<16, true, kCausal, false>(t_s, t_dp, t_ps, t_ds_k, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
         }
       }
       tmem_st_wait();
@@ -480,10 +581,15 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
       wait_bounded(bar_o, ph & 1);
       tc_fence_after();
       __nv_bfloat16* drow = dqkv + ((long long)seq * L + row) * ld3 + h * 64;
+      // the accumulators are copied to registers, the TMEM columns handed back to the MMA warp (next phase's
+      // S / dP MMAs start), and only then do the global stores run
       if (qlanes) {  // dQ: each warp of the pair writes 32 of the 64 dims
         uint32_t a[32];
         tmem_ld_32x32(tl + kColOutA + hh * 32, a);
         tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_e);
         if (row < L) store_row32(drow + hh * 32, a, scale);
       } else {       // hh = 0: dV, hh = 1: dK (scaled)
         uint32_t a[32], b[32];
@@ -491,11 +597,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
         tmem_ld_32x32(tl + col, a);
         tmem_ld_32x32(tl + col + 32, b);
         tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_e);
         if (row < L) store_row64(drow + (hh ? D : 2 * D), a, b, hh ? scale : 1.f);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_e);
     }
   }
   tc_fence_before();

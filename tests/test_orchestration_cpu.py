@@ -176,3 +176,71 @@ def test_class_sharded_data_parallel_step_world2_gloo(focal):
         assert float((o["grad"] - ref["grad"]).abs().max()) < 1e-4 * float(ref["grad"].abs().max())
         assert float((o["param"] - ref["param"]).abs().max()) < 0.0025 * 2e-4 * float(ref["grad"].abs().max()) + 1e-7
     assert float((out[0]["param"] - out[1]["param"]).abs().max()) == 0.0         # ranks stay bit-identical
+
+
+def _sharded_worker_other(rank, world, port, kind, tokens, B_global, out):
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        TorchKernels().install(_Patch())
+        from psrc_b200 import synthetic as S
+        C = tokens.shape[0]
+        alpha = S.focal_alpha(list(range(1, C + 1)), C)
+        image, label = S.synthetic_batch(B_global, C, 64, seed=1)
+        Bl = B_global // world
+
+        def build(batch, w, r, pg):
+            if kind == "maple":
+                return maple_setup("tiny", 3, tokens, "cpu", "fp32", batch=batch, world=w, rank=r, pg=pg,
+                                   focal_alpha=alpha)[0]
+            return cocoop_setup("tiny", tokens, "cpu", "fp32", batch=batch, world=w, rank=r, pg=pg,
+                                focal_alpha=alpha)[0]
+        step = build(Bl, world, rank, dist.group.WORLD)
+        step.image.copy_(image[rank * Bl:(rank + 1) * Bl])
+        step.labels.copy_(label[rank * Bl:(rank + 1) * Bl].int())
+        step.forward_backward()
+        step.init_optimizer()
+        step.sgd()
+        res = {"grad": step.flat_grad.clone(), "losses": step.losses.clone(), "param": step.flat_param.clone(),
+               "logits": step.logits.clone(), "classes": (step.c0, step.c1)}
+        if rank == 0:
+            ref = build(B_global, 1, 0, None)
+            ref.image.copy_(image)
+            ref.labels.copy_(label.int())
+            ref.forward_backward()
+            ref.init_optimizer()
+            ref.sgd()
+            res["ref"] = {"grad": ref.flat_grad.clone(), "losses": ref.losses.clone(), "param": ref.flat_param.clone(),
+                          "logits": ref.logits.clone()}
+        out[rank] = res
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("kind", ["maple", "cocoop"])
+def test_maple_cocoop_sharded_step_world2_gloo(kind):
+    """MaPLe: class-sharded text tower + data-parallel images, the coupling-Linear gradients receive contributions
+    from both sides before the all-reduce.  CoCoOp: pure batch sharding (every rank runs all classes for its images),
+    only the all-reduce of ctx + meta-net gradients.  Both must equal the single-process step."""
+    from psrc_b200 import synthetic as S
+    tokens = S.synthetic_tokens(10, name_lens=[1, 2, 3, 8, 1, 1, 2, 2, 1, 2])
+    world, B_global = 2, 4
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_sharded_worker_other, args=(world, _free_port(), kind, tokens, B_global, out), nprocs=world, join=True)
+    ref = out[0]["ref"]
+    want = [(0, 10), (0, 10)] if kind == "cocoop" else [(0, 5), (5, 10)]
+    assert [out[r]["classes"] for r in range(world)] == want
+    Bl = B_global // world
+    for r in range(world):
+        o = out[r]
+        assert float((o["logits"] - ref["logits"][r * Bl:(r + 1) * Bl]).abs().max()) < 1e-5
+        assert float((o["losses"] - ref["losses"]).abs().max()) < 1e-5, (o["losses"], ref["losses"])
+        assert cos(o["grad"], ref["grad"]) > 0.999999
+        assert float((o["grad"] - ref["grad"]).abs().max()) < 1e-4 * float(ref["grad"].abs().max())
+    assert float((out[0]["param"] - out[1]["param"]).abs().max()) == 0.0
