@@ -5,7 +5,8 @@
 // stage) -- so every operand byte is fetched from L2 once per pair and each SM reads only half of W from
 // shared memory per MMA -- and the leader CTA's elected thread issues tcgen05.mma.cta_group::2
 // (UMMA 256 x BN x 16, bf16 in, fp32 accumulators in the TMEM of both SMs, two accumulator stages).
-// Epilogue (both CTAs, warps 4..7, one TMEM lane = one output row per thread):
+// Epilogue (both CTAs, warps 4..11: two warps per TMEM lane quarter taking the even / odd 32-column chunks, one
+// TMEM lane = one output row per thread):
 //   tcgen05.ld 32 columns -> registers -> fused bias / QuickGELU / QuickGELU' * aux / + residual ->
 //   bank-conflict-free swizzled shared-memory staging -> TMA bulk tensor store (coalesced, asynchronous).
 // The fp32 residual / bf16 aux operands are prefetched by a dedicated warp with TMA into a ring of
@@ -25,8 +26,9 @@ namespace pair {
 constexpr int kBMcta = 128;     // rows per CTA (UMMA M = 256 over the pair)
 constexpr int kBK = 64;         // K per stage: 64 bf16 = 128 B = one swizzle atom row
 constexpr int kUmmaK = 16;
-constexpr int kThreads = 256;
-constexpr int kInSlots = 3;     // ring of prefetched residual / aux chunks (128 rows x 32 columns each)
+constexpr int kEpiWarps = 8;    // two epilogue warps per TMEM lane quarter: even / odd 32-column chunks
+constexpr int kThreads = (4 + kEpiWarps) * 32;
+constexpr int kInSlots = 4;     // ring of prefetched residual / aux chunks (128 rows x 32 columns each)
 constexpr int kInSlotBytes = 128 * 128;   // fp32 chunk; a bf16 chunk uses the first half
 constexpr int kOutSlotBytes = 32 * 128;   // per epilogue warp: 32 rows x 32 fp32 (or bf16 out + bf16 out2)
 constexpr uint32_t kSpinLimit = 1u << 27;
@@ -56,7 +58,7 @@ struct Smem {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kInOffset = STAGES * kStageBytes;
   static constexpr int kOutOffset = kInOffset + kInSlots * kInSlotBytes;
-  static constexpr int kBarOffset = kOutOffset + 4 * 2 * kOutSlotBytes;
+  static constexpr int kBarOffset = kOutOffset + kEpiWarps * kOutSlotBytes;   // one staging slot per epilogue warp
   // full[STAGES] empty[STAGES] tmem_full[2] tmem_empty[2] in_full[kInSlots] in_empty[kInSlots] + tmem slot
   static constexpr int kNumBars = 2 * STAGES + 4 + 2 * kInSlots;
   static constexpr int kTotal = kBarOffset + kNumBars * 8 + 16;
@@ -121,7 +123,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);   // multicast tcgen05.commit
-      mbar_init(&tmem_empty[s], 8);  // 4 epilogue warps x 2 CTAs (leader's copy is the one used)
+      mbar_init(&tmem_empty[s], 2 * kEpiWarps);  // epilogue warps x 2 CTAs (leader's copy is the one used)
     }
     for (int s = 0; s < kInSlots; ++s) {
       mbar_init(&in_full[s], 1);
@@ -211,29 +213,24 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   } else if (warp >= 4) {
     // ===================== epilogue warps (TMEM -> regs -> swizzled smem -> TMA store) =====================
     const int q = warp & 3;                 // TMEM lane quarter this warp may access
+    const int par = (warp - 4) >> 2;        // this warp takes the chunks with c % 2 == par
     const int r_cta = q * 32 + lane;        // row inside this CTA's 128-row half
-    uint8_t* out_slots = smem + S::kOutOffset + q * 2 * kOutSlotBytes;
+    uint8_t* oslot = smem + S::kOutOffset + (warp - 4) * kOutSlotBytes;
     int as = 0;
     uint32_t aphase = 0;
-    int islot = 0;
-    uint32_t iphase = 0;
-    uint32_t oc = 0;                        // running chunk counter (output staging slot = oc & 1)
+    uint32_t gbase = 0;                     // chunks the prefetch warp has issued before this tile (ring position)
     for (int tile = pair_id; tile < num_tiles; tile += n_pairs) {
       const int m_blk = tile / p.tiles_n, n_blk = tile % p.tiles_n;
       const int row0 = m_blk * 256 + (int)rank * kBMcta + q * 32;   // first row of this warp's 32-row box
       wait_bounded(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
+      const int tile_chunks = min(kChunks, (p.N - n_blk * BN + 31) >> 5);
 #pragma unroll 1
-      for (int c = 0; c < kChunks; ++c) {
+      for (int c = par; c < tile_chunks; c += 2) {
         const int col0 = n_blk * BN + c * 32;
-        if (col0 >= p.N) break;  // warp-uniform
         uint32_t r[32];
         tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
-        // the staging slot written two chunks ago must have been read by its TMA store
-        if (lane == 0) bulk_wait_read<1>();
-        __syncwarp();
-        uint8_t* oslot = out_slots + (oc & 1) * kOutSlotBytes;
         float v[32];
         tmem_ld_wait();
         if (p.bias) {
@@ -251,7 +248,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           for (int i = 0; i < 32; ++i) v[i] = p.alpha * __uint_as_float(r[i]);
         }
         if (kHasIn) {
-          wait_bounded(&in_full[islot], iphase);
+          const uint32_t g = gbase + (uint32_t)c;              // position of this chunk in the prefetch ring
+          const int islot = (int)(g % kInSlots);
+          wait_bounded(&in_full[islot], (g / kInSlots) & 1u);
           const uint8_t* in = smem + S::kInOffset + islot * kInSlotBytes;
           if (MODE == kResidual) {
 #pragma unroll
@@ -274,8 +273,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           }
           __syncwarp();
           if (lane == 0) mbar_arrive(&in_empty[islot]);
-          if (++islot == kInSlots) { islot = 0; iphase ^= 1; }
         }
+        // this warp's staging slot must have been read by the TMA store of its previous chunk
+        if (lane == 0) bulk_wait_read<0>();
+        __syncwarp();
         if (MODE == kGelu) {
           if (p.has_out2) {  // pre-activation copy for the backward (second half of the slot)
 #pragma unroll
@@ -312,8 +313,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if (MODE == kGelu && p.has_out2) tma_store_2d(&tmap_out2, oslot + 2048, col0, row0);
           bulk_commit();
         }
-        ++oc;
       }
+      gbase += (uint32_t)tile_chunks;
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_leader(&tmem_empty[as]);   // release this accumulator stage to the leader's MMA
@@ -429,7 +430,7 @@ static int launch_bn(const psrc_gemm_args& a, cudaStream_t stream) {
   // 256 x 256 tiles always (measured: UMMA 256x128 is shared-memory-bandwidth bound, 830 vs 1230 TFLOP/s on the
   // QKV shape); 256 x 128 only when N itself is that narrow.  PSRC_PAIR_BN is a tuning knob.
   static const int force_bn = getenv("PSRC_PAIR_BN") ? atoi(getenv("PSRC_PAIR_BN")) : 0;
-  if (force_bn == 128 || (force_bn == 0 && a.N <= 128)) return launch<128, 6, MODE, OUT_BYTES>(a, stream);
+  if (force_bn == 128 || (force_bn == 0 && a.N <= 128)) return launch<128, 5, MODE, OUT_BYTES>(a, stream);
   return launch<256, 4, MODE, OUT_BYTES>(a, stream);
 }
 
