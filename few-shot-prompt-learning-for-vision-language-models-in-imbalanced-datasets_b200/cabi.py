@@ -77,6 +77,7 @@ SIGNATURES = {
     "psrc_group_logits_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     "psrc_group_logits_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     "psrc_ctx_bias_grad": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "psrc_permute_rows": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
 }
 
 _lib = None

@@ -138,9 +138,45 @@ __global__ void ctx_bias_grad_kernel(const float* __restrict__ gg, float* __rest
   }
 }
 
+// CoOp CLASS_TOKEN_POSITION middle / front (coop.py:278-293): the prompt of class s is the 'end' layout with its rows
+// permuted.  forward: dst[s,p,:] = src[s,perm[s,p],:] (+ add[p,:]);  inverse (the backward): dst[s,perm[s,p],:] = src[s,p,:]
+__global__ void permute_rows_kernel(const float4* __restrict__ src, const int32_t* __restrict__ perm,
+                                    const float4* __restrict__ add, float4* __restrict__ dst, int n_seq, int L, int D4,
+                                    int inverse) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)n_seq * L * D4) return;
+  const int d = (int)(i % D4);
+  const long long row = i / D4;
+  const int p = (int)(row % L);
+  const long long s = row / L;
+  const int q = perm[row];
+  if (inverse) {
+    dst[(s * L + q) * D4 + d] = src[i];
+  } else {
+    float4 v = src[(s * L + q) * D4 + d];
+    if (add) {
+      const float4 a = add[(long long)p * D4 + d];
+      v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+    }
+    dst[i] = v;
+  }
+}
+
 }  // namespace psrc
 
 using namespace psrc;
+
+extern "C" int psrc_permute_rows(const float* src, const int32_t* perm, const float* add, float* dst, int n_seq, int L,
+                                 int D, int inverse, psrc_stream_t stream) {
+  PSRC_CHECK_ARG(src && perm && dst && src != dst && n_seq > 0 && L > 0 && D > 0 && D % 4 == 0,
+                 "psrc_permute_rows: bad arguments");
+  const long long n = (long long)n_seq * L * (D / 4);
+  permute_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(
+      reinterpret_cast<const float4*>(src), perm, reinterpret_cast<const float4*>(add),
+      reinterpret_cast<float4*>(dst), n_seq, L, D / 4, inverse);
+  PSRC_CHECK_LAUNCH();
+  return PSRC_OK;
+}
 
 static inline unsigned blocks_for(long long n, int block) { return (unsigned)((n + block - 1) / block); }
 

@@ -244,3 +244,11 @@ def ctx_bias_grad(gg, dctx, dbias):
     _f32c(gg, dctx, dbias)
     cabi.check(cabi.load().psrc_ctx_bias_grad(ptr(gg), ptr(dctx), ptr(dbias), G, n_ctx, D, cabi.stream()),
                "psrc_ctx_bias_grad")
+
+
+def permute_rows(src, perm, dst, n_seq, L, D, add=None, inverse=False):
+    assert src.shape == dst.shape == (n_seq * L, D) and perm.shape == (n_seq, L) and perm.dtype == torch.int32
+    _f32c(src, dst, add)
+    cabi.check(cabi.load().psrc_permute_rows(ptr(src), ptr(perm), ptr(add), ptr(dst), n_seq, L, D, int(inverse),
+                                             cabi.stream()), "psrc_permute_rows")
+    return dst

@@ -42,6 +42,7 @@ class StepConfig:
     focal_alpha: list | None = None  # imbalance-aware CE (coop.py:326-346); None -> plain CE
     focal_gamma: float = 2.0
     truncate_text: bool = True      # run text positions 0..max(EOT) only (exact)
+    class_token_position: str = "end"   # CoOp: "end" | "middle" | "front" (coop.py:267-293)
     coupling: bool = False          # MaPLe: vision prompts = Linear_i(text prompts) (maple.py:145, :155-156, :199-204)
     per_image_text: bool = False    # CoCoOp: one text-encoder pass per image, ctx + meta_net(f_hat) (cocoop.py:173-198)
     meta_hidden: int = 0            # CoCoOp meta-net hidden width (vis_dim // 16, cocoop.py:139-143)
@@ -139,6 +140,23 @@ class PromptedClipStep:
         self.token_prefix = _dev(emb[:, :1], dev)                           # promptsrc.py:136
         self.token_suffix = _dev(emb[:, 1 + cfg.n_ctx_text:], dev)          # promptsrc.py:137
         self.eot = eot_all[self.c0:self.c1].to(torch.int32).to(dev)
+        # CoOp class-token positions other than "end": the prompt is the "end" layout with its rows permuted per class
+        self.text_perm = None
+        if cfg.class_token_position != "end":
+            assert cfg.class_token_position in ("middle", "front"), cfg.class_token_position
+            assert cfg.depth_text == 1 and not self.per_image, "class-token positions are a CoOp option (coop.py:267)"
+            perm = torch.arange(self.Lt, dtype=torch.int32).repeat(self.Cl, 1)
+            n_c = cfg.n_ctx_text
+            for i, e_ in enumerate(eot_all[self.c0:self.c1].tolist()):
+                name_len = e_ - n_c - 2                                      # SOT, ctx, name tokens, ".", EOT
+                assert name_len >= 0
+                ctx_pos = list(range(1, 1 + n_c))
+                cls_pos = list(range(1 + n_c, 1 + n_c + name_len))
+                half = n_c // 2
+                order = (ctx_pos[:half] + cls_pos + ctx_pos[half:]) if cfg.class_token_position == "middle" \
+                    else (cls_pos + ctx_pos)                                 # coop.py:268-281 / :282-291
+                perm[i, 1:1 + len(order)] = torch.tensor(order, dtype=torch.int32)
+            self.text_perm = perm.to(dev)
         self.n_text_seq = self.Cl * (B if self.per_image else 1)
         if self.per_image:
             self.eot = self.eot.repeat(B).contiguous()                       # sequence s = image * C + class
@@ -171,6 +189,9 @@ class PromptedClipStep:
         self.df_a = e(B, self.E, dt=self.act) if self.act != torch.float32 else self.df
         self.dt_a = e(Ts, self.E, dt=self.act) if self.act != torch.float32 else self.dt_
         self.dhv, self.dht = e(B, self.Dv, dt=self.act), e(Ts, self.Dt, dt=self.act)
+        if self.text_perm is not None:
+            self.x0_end, self.dx0_end = e(self.Cl * self.Lt, self.Dt), e(self.Cl * self.Lt, self.Dt)
+            self.zero_pos = torch.zeros_like(self.tpos)
         self.losses = e(4)
         self.loss_scratch = e(4 * B + 2 * 296)
         self.labels = torch.zeros(B, device=dev, dtype=torch.int32)
@@ -281,6 +302,10 @@ class PromptedClipStep:
             ops.assemble_text_prompts(self.token_prefix, self.token_suffix, ctx, self.tpos, self.tt.x0, self.Cl,
                                       self.Lt, cfg.n_ctx_text, self.Dt, ctx_bias=self.ctx_bias.view(cfg.batch, self.Dt),
                                       n_groups=cfg.batch)
+        elif self.text_perm is not None:
+            ops.assemble_text_prompts(self.token_prefix, self.token_suffix, ctx, self.zero_pos, self.x0_end, self.Cl,
+                                      self.Lt, cfg.n_ctx_text, self.Dt, ctx_per_class=cfg.ctx_per_class)
+            ops.permute_rows(self.x0_end, self.text_perm, self.tt.x0, self.Cl, self.Lt, self.Dt, add=self.tpos)
         else:
             ops.assemble_text_prompts(self.token_prefix, self.token_suffix, ctx, self.tpos, self.tt.x0, self.Cl,
                                       self.Lt, cfg.n_ctx_text, self.Dt, ctx_per_class=cfg.ctx_per_class)
@@ -424,12 +449,17 @@ class PromptedClipStep:
                                  dw=g_["meta.w2"].unsqueeze(0), db=g_["meta.b2"].unsqueeze(0))
             ops.small_linear_bwd(self.f_hat.view(1, B, self.E), p["meta.w1"].unsqueeze(0), self.meta_dh,
                                  dw=g_["meta.w1"].unsqueeze(0), db=g_["meta.b1"].unsqueeze(0), y_relu=self.meta_h)
+        dx0 = self.tt.dx
+        if self.text_perm is not None:          # route d(x0) back to the "end" layout the context rows live in
+            dx0 = ops.permute_rows(self.tt.dx, self.text_perm, self.dx0_end, self.Cl, self.Lt, self.Dt, inverse=True)
+        if self.per_image:
+            pass
         elif cfg.ctx_per_class:
             g = self.grads["ctx"]
             g.zero_()
-            g[self.c0:self.c1].copy_(self.tt.dx.view(self.Cl, self.Lt, self.Dt)[:, 1:1 + cfg.n_ctx_text])
+            g[self.c0:self.c1].copy_(dx0.view(self.Cl, self.Lt, self.Dt)[:, 1:1 + cfg.n_ctx_text])
         else:
-            ops.prompt_grad(self.tt.dx, self.grads["ctx"], self.Cl, self.Lt, 1, cfg.n_ctx_text, self.Dt,
+            ops.prompt_grad(dx0, self.grads["ctx"], self.Cl, self.Lt, 1, cfg.n_ctx_text, self.Dt,
                             zero_rows=False, round_fp16=False)               # ctx has no .half() (promptsrc.py:160)
         # ---- vision side (only when vision prompts exist)
         if cfg.n_ctx_vision > 0:

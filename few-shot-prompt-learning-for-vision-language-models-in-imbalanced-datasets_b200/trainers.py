@@ -504,7 +504,7 @@ def _focal(logits, label, st):
 
 
 class CoOpCustomCLIP(_CustomCLIPBase):
-    """CustomCLIP of trainers/coop.py:302-390 for LOSS_TYPE ce / focal, CLASS_TOKEN_POSITION 'end'."""
+    """CustomCLIP of trainers/coop.py:302-390 for LOSS_TYPE ce / focal, CLASS_TOKEN_POSITION end / middle / front."""
 
     def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None):
         super().__init__()
@@ -513,8 +513,9 @@ class CoOpCustomCLIP(_CustomCLIPBase):
         self.loss_type = _get(T, "LOSS_TYPE", "ce")
         if self.loss_type not in ("ce", "focal"):
             raise NotImplementedError("LOSS_TYPE simclr (coop.py:316-321) is outside the accelerated path")
-        if _get(T, "CLASS_TOKEN_POSITION", "end") != "end":
-            raise NotImplementedError("CLASS_TOKEN_POSITION middle/front (coop.py:278-293) is not accelerated yet")
+        position = _get(T, "CLASS_TOKEN_POSITION", "end")
+        if position not in ("end", "middle", "front"):
+            raise ValueError("Unknown class_token_position")                 # coop.py:293
         n_ctx, ctx_init, csc = int(T.N_CTX), _get(T, "CTX_INIT", ""), bool(_get(T, "CSC", False))
         names = [n.replace("_", " ") for n in classnames]
         sd_emb = clip_model.state_dict()["token_embedding.weight"].detach().float().cpu()
@@ -534,7 +535,7 @@ class CoOpCustomCLIP(_CustomCLIPBase):
             ctx_vectors = torch.empty(*shape)
             nn.init.normal_(ctx_vectors, std=0.02)
         kw = dict(prec_cfg=T.PREC, n_ctx_text=n_ctx, n_ctx_vision=0, depth_text=1, depth_vision=0,
-                  ctx_per_class=csc, zero_shot_branch=False)
+                  ctx_per_class=csc, zero_shot_branch=False, class_token_position=position)
         if self.loss_type == "focal":
             kw["focal_alpha"] = _focal_alpha_from_cfg(cfg, len(classnames))
         self._build(cfg, clip_model, tokens, kw, ctx_vectors, device=device)

@@ -212,6 +212,14 @@ int psrc_group_logits_bwd(const float* f_hat, const float* d_logits, float* d_th
 int psrc_ctx_bias_grad(const float* gg, float* dctx, float* dbias, int G, int n_ctx, int D,
                        psrc_stream_t stream);
 
+/* CoOp CLASS_TOKEN_POSITION "middle" / "front" (PromptSRC/trainers/coop.py:278-293): the prompt of class s is the
+ * "end" layout [prefix | ctx | class tokens | rest] with its rows permuted (per-class, because the class-name length
+ * differs).  perm int32 [n_seq, L], a bijection of [0, L) per sequence.
+ *   inverse == 0: dst[s,p,:] = src[s,perm[s,p],:] (+ add[p,:], the positional embedding, may be NULL)
+ *   inverse != 0: dst[s,perm[s,p],:] = src[s,p,:]   (autograd of the gather: routes d(x0) back to the "end" layout) */
+int psrc_permute_rows(const float* src, const int32_t* perm, const float* add, float* dst,
+                      int n_seq, int L, int D, int inverse, psrc_stream_t stream);
+
 /* ------------------------------------------------------------------- loss
  * PromptSRC objective and its gradient in one pass (promptsrc.py:204, :304-324;
  * focal CE: coop.py:146-163 / promptsrc_pets_focal.py:93-117):

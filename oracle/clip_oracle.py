@@ -173,20 +173,42 @@ def teacher_text_features(sd, teacher_tokens, text_heads, truncate=None):
         return text_tower(emb, teacher_tokens.argmax(-1), sd, text_heads, truncate=truncate)
 
 
-def clip_logits(sd, tokens, image, ctx, n_ctx, vision_heads, text_heads, truncate=None, ctx_per_class=False):
-    """CoOp CustomCLIP.forward_once, trainers/coop.py:351-365 (class_token_position 'end', :270-276)."""
+def construct_prompts_positioned(prefix, ctx, suffix, name_lens, position):
+    """PromptLearner.forward of CoOp for class_token_position middle / front (trainers/coop.py:268-291)."""
+    C = prefix.shape[0]
+    if ctx.dim() == 2:
+        ctx = ctx.unsqueeze(0).expand(C, -1, -1)
+    half = ctx.shape[1] // 2
+    rows = []
+    for i in range(C):
+        nl = int(name_lens[i])
+        cls_i, suf_i = suffix[i:i + 1, :nl], suffix[i:i + 1, nl:]
+        if position == "middle":
+            rows.append(torch.cat([prefix[i:i + 1], ctx[i:i + 1, :half], cls_i, ctx[i:i + 1, half:], suf_i], dim=1))
+        else:
+            rows.append(torch.cat([prefix[i:i + 1], cls_i, ctx[i:i + 1], suf_i], dim=1))
+    return torch.cat(rows, dim=0)
+
+
+def clip_logits(sd, tokens, image, ctx, n_ctx, vision_heads, text_heads, truncate=None, ctx_per_class=False,
+                position="end"):
+    """CoOp CustomCLIP.forward_once, trainers/coop.py:351-365 (class_token_position 'end' :267, 'middle' :268-281,
+    'front' :282-291; name_lens = tokens of the class name = EOT index - n_ctx - 2)."""
     emb = sd["token_embedding.weight"][tokens]
     prefix, suffix = emb[:, :1], emb[:, 1 + n_ctx:]                 # coop.py:247-248
-    prompts = construct_prompts(prefix, ctx, suffix)
+    if position == "end":
+        prompts = construct_prompts(prefix, ctx, suffix)
+    else:
+        prompts = construct_prompts_positioned(prefix, ctx, suffix, tokens.argmax(-1) - n_ctx - 2, position)
     f_hat = normalize(vision_tower(image, sd, vision_heads))
     t_hat = normalize(text_tower(prompts, tokens.argmax(-1), sd, text_heads, truncate=truncate))
     return sd["logit_scale"].exp() * f_hat @ t_hat.t()
 
 
 def coop_step(sd, tokens, image, label, ctx, n_ctx, vision_heads, text_heads, focal_alpha=None, use_focal=False,
-              truncate=None):
+              truncate=None, position="end"):
     """coop.py:380-385: criterion_ce(logits, lbl) with CE (:323) or MultiClassFocalLoss (:346)."""
-    logits = clip_logits(sd, tokens, image, ctx, n_ctx, vision_heads, text_heads, truncate)
+    logits = clip_logits(sd, tokens, image, ctx, n_ctx, vision_heads, text_heads, truncate, position=position)
     loss = focal_ce(logits, label, focal_alpha) if use_focal else F.cross_entropy(logits, label)
     return {"loss": loss, "logits": logits}
 

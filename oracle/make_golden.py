@@ -37,6 +37,10 @@ CASES = {
     "cfg1_promptsrc": ("PromptSRC", "ViT-B/16", [f"object {i}" for i in range(100)], 4, 9, {}),
     "tiny_coop_ce": ("CoOp", "tiny", RAGGED_NAMES, 5, 0, {"TRAINER.COOP.LOSS_TYPE": "ce"}),
     "tiny_coop_focal": ("CoOp", "tiny", RAGGED_NAMES, 5, 0, {"TRAINER.COOP.LOSS_TYPE": "focal"}),
+    "tiny_coop_middle": ("CoOp", "tiny", RAGGED_NAMES, 5, 0, {"TRAINER.COOP.LOSS_TYPE": "ce",
+                                                              "TRAINER.COOP.CLASS_TOKEN_POSITION": "middle"}),
+    "tiny_coop_front": ("CoOp", "tiny", RAGGED_NAMES, 5, 0, {"TRAINER.COOP.LOSS_TYPE": "focal",
+                                                             "TRAINER.COOP.CLASS_TOKEN_POSITION": "front"}),
     # MaPLe hard-codes the ViT-B widths 768 / 512 (maple.py:144-156): full-size towers, few classes
     "vitb_maple_ce": ("MaPLe", "ViT-B/16", RAGGED_NAMES, 2, 3, {}),
     "vitb_maple_focal": ("MaPLe", "ViT-B/16", RAGGED_NAMES, 2, 3, {"TRAINER.MAPLE.USE_FOCAL_LOSS": True}),
@@ -154,8 +158,10 @@ def run_coop(name, arch_name, classnames, batch, extra):
     use_focal = extra.get("TRAINER.COOP.LOSS_TYPE") == "focal"
     alpha = torch.tensor(S.focal_alpha(shots, len(classnames))) if use_focal else None
     ctx = ctx0.clone().requires_grad_(True)
+    position = extra.get("TRAINER.COOP.CLASS_TOKEN_POSITION", "end")
+    assert model.prompt_learner.name_lens == (tokens.argmax(-1) - n_ctx - 2).tolist()   # name length from the EOT index
     o = O.coop_step(sd, tokens, image, label, ctx, n_ctx, arch.vision_heads, arch.transformer_heads,
-                    focal_alpha=alpha, use_focal=use_focal)
+                    focal_alpha=alpha, use_focal=use_focal, position=position)
     o["loss"].backward()
     print(f"[{name}] reference loss={float(loss):.6f}; oracle |d|={abs(float(o['loss']) - float(loss)):.2e} "
           f"grad cos={cos(ctx.grad, grad):.7f} rel={rel(ctx.grad, grad):.2e}")

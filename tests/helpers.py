@@ -92,6 +92,21 @@ def maple_setup(arch_name, depth, tokens, device, prec, batch, n_ctx=2, sd=None,
     return step, sd, mp_
 
 
+def coop_setup(arch_name, tokens, device, prec, batch, ctx0, n_ctx=16, sd=None, focal_alpha=None, position="end"):
+    """The CoOp configuration of oracle/make_golden.py:run_coop (16 generic context tokens, seeded ctx from the fixture)."""
+    from psrc_b200 import synthetic as S
+    from psrc_b200.step import PromptedClipStep, StepConfig
+    arch = S.ARCHS[arch_name]
+    sd = sd if sd is not None else S.make_clip_state_dict(arch, seed=0)
+    tokens = torch.as_tensor(np.asarray(tokens)).long()
+    cfg = StepConfig(arch=arch, n_cls=tokens.shape[0], batch=batch, prec=prec, n_ctx_text=n_ctx, n_ctx_vision=0,
+                     depth_text=1, depth_vision=0, focal_alpha=focal_alpha, class_token_position=position)
+    step = PromptedClipStep(cfg, sd, tokens, device)
+    with torch.no_grad():
+        step.params["ctx"].copy_(torch.as_tensor(ctx0))
+    return step, sd
+
+
 COCOOP_REF = {"ctx": "prompt_learner.ctx", "meta.w1": "prompt_learner.meta_net.linear1.weight",
               "meta.b1": "prompt_learner.meta_net.linear1.bias", "meta.w2": "prompt_learner.meta_net.linear2.weight",
               "meta.b2": "prompt_learner.meta_net.linear2.bias"}
@@ -135,8 +150,13 @@ class FakeKernels:
                      "im2col_patches", "assemble_vision_tokens", "assemble_text_prompts", "insert_prompt",
                      "prompt_grad", "gather_ln_fwd", "gather_ln_bwd", "l2norm_fwd", "l2norm_bwd", "loss_fwd_bwd",
                      "sgd_step", "cast", "axpy", "small_linear_fwd", "small_linear_bwd", "group_logits_fwd",
-                     "group_logits_bwd", "ctx_bias_grad"):
+                     "group_logits_bwd", "ctx_bias_grad", "permute_rows"):
             monkeypatch.setattr(ops, name, getattr(self, name))
+
+    def permute_rows(self, src, perm, dst, n_seq, L, D, add=None, inverse=False):
+        self._rec("permute_rows")
+        assert src.shape == dst.shape == (n_seq * L, D) and perm.shape == (n_seq, L)
+        return dst
 
     def small_linear_fwd(self, x, w, b, y, relu=False):
         self._rec("small_linear_fwd")

@@ -18,7 +18,7 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
     if p not in sys.path:
         sys.path.insert(0, p)
 
-from helpers import (COCOOP_REF, cocoop_setup, cos, load_golden, maple_ref_name, maple_setup,  # noqa: E402
+from helpers import (COCOOP_REF, cocoop_setup, coop_setup, cos, load_golden, maple_ref_name, maple_setup,  # noqa: E402
                      promptsrc_setup, ref_name)
 
 CASES = {"tiny_promptsrc": ("tiny", 3), "cfg1_promptsrc": ("ViT-B/16", 9)}
@@ -168,6 +168,62 @@ def run_cocoop_case(name: str, prec: str) -> dict:
     return _generic_metrics(step, fx, lambda k: COCOOP_REF[k], 0.002, dev)
 
 
+def run_coop_case(name: str, prec: str) -> dict:
+    """CoOp (tiny architecture; class token position end / middle / front) against tests/golden/tiny_coop_*.npz."""
+    from psrc_b200 import synthetic as S
+    fx = load_golden(name)
+    dev = "cuda"
+    B, C = fx["label"].shape[0], fx["tokens"].shape[0]
+    focal = name.endswith("focal") or name.endswith("front")
+    position = {"tiny_coop_middle": "middle", "tiny_coop_front": "front"}.get(name, "end")
+    alpha = S.focal_alpha(fx["shots"].tolist(), C) if focal else None
+    step, sd = coop_setup("tiny", fx["tokens"], dev, prec, B, fx["ctx0"], focal_alpha=alpha, position=position)
+    image, label = S.synthetic_batch(B, C, 64, seed=2)
+    assert np.array_equal(label.numpy().astype(np.int32), fx["label"])
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    torch.cuda.synchronize()
+    return _generic_metrics(step, fx, lambda k: "prompt_learner.ctx", 0.002, dev)
+
+
+def run_maple_vitl_case(name: str, prec: str) -> dict:
+    """BASELINE config #5's architecture (MaPLe on ViT-L/14: vision 1024 x 24 layers x 16 heads, 257 + 2 tokens; text
+    768 x 12 heads) against the oracle restatement run on the CPU in this process -- the reference itself cannot
+    express it (768 / 512 hard-coded, no ViT-L/14 in clip._MODELS), so there is no golden file."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import clip_oracle as O
+    from psrc_b200 import ops, synthetic as S
+    dev, arch = "cuda", S.ARCHS["ViT-L/14"]
+    depth, n_ctx, B = 3, 2, 2
+    tokens = S.synthetic_tokens(10, name_lens=[1, 2, 3, 8, 1, 1, 2, 2, 1, 2])
+    C = tokens.shape[0]
+    step, sd, _ = maple_setup("ViT-L/14", depth, tokens, dev, prec, batch=B, n_ctx=n_ctx)
+    image, label = S.synthetic_batch(B, C, arch.image_resolution, seed=3)
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    torch.cuda.synchronize()
+    P = {k: step.params[k].detach().cpu().clone().requires_grad_(True) for k in step.params}
+    torch.set_num_threads(os.cpu_count() or 1)
+    o = O.maple_step(sd, torch.as_tensor(tokens), image, label, P["ctx"], [P[f"text.{i}"] for i in range(1, depth)],
+                     (P["couple.w.0"], P["couple.b.0"]),
+                     [(P[f"couple.w.{i}"], P[f"couple.b.{i}"]) for i in range(1, depth)], n_ctx, arch.vision_heads,
+                     arch.transformer_heads, truncate=int(torch.as_tensor(tokens).argmax(-1).max()) + 1)
+    o["loss"].backward()
+    m = {"logits_maxabs": float((step.logits.cpu() - o["logits"].detach()).abs().max())}
+    loss = float(step.losses.sum())
+    m["loss"], m["loss_rel"] = loss, abs(loss - float(o["loss"].detach())) / abs(float(o["loss"].detach()))
+    cs = {k: cos(step.grads[k], P[k].grad) for k in step.params}
+    m["gradcos_worst_key"] = min(cs, key=cs.get)
+    m["gradcos_worst"] = cs[m["gradcos_worst_key"]]
+    m["gradcos_all"] = cos(torch.cat([step.grads[k].flatten().cpu() for k in step.params]),
+                           torch.cat([P[k].grad.flatten() for k in step.params]))
+    m["param_update_cos"] = m["gradcos_all"]
+    m["vision_seq_len"], m["text_width"] = step.Lv, step.Dt
+    return m
+
+
 def check_generic(m: dict, prec: str, name: str = "") -> list[str]:
     t = TOL_TINY_BF16 if (prec == "bf16" and name.startswith("tiny")) else TOL[prec]
     bad = []
@@ -185,7 +241,10 @@ def check_generic(m: dict, prec: str, name: str = "") -> list[str]:
 
 
 OTHER_CASES = {"vitb_maple_ce": run_maple_case, "vitb_maple_focal": run_maple_case,
-               "tiny_cocoop_ce": run_cocoop_case, "tiny_cocoop_focal": run_cocoop_case}
+               "tiny_cocoop_ce": run_cocoop_case, "tiny_cocoop_focal": run_cocoop_case,
+               "vitl_maple_oracle": run_maple_vitl_case,
+               "tiny_coop_ce": run_coop_case, "tiny_coop_focal": run_coop_case, "tiny_coop_middle": run_coop_case,
+               "tiny_coop_front": run_coop_case}
 
 
 def check(m: dict, prec: str, name: str = "") -> list[str]:

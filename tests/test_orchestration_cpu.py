@@ -11,7 +11,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from helpers import COCOOP_REF, cocoop_setup, cos, load_golden, maple_ref_name, maple_setup, promptsrc_setup, ref_name
+from helpers import COCOOP_REF, cocoop_setup, coop_setup, cos, load_golden, maple_ref_name, maple_setup, promptsrc_setup, ref_name
 from torch_kernels import TorchKernels
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -45,6 +45,31 @@ def test_step_orchestration_matches_reference_golden(monkeypatch):
     assert np.array_equal(step.logits.argmax(1).numpy().astype(np.int32), fx["argmax"])
     for k in step.params:
         assert cos(step.grads[k], fx["grad/" + ref_name(k)]) > 0.99999, k
+
+
+@pytest.mark.parametrize("name,focal,position", [("tiny_coop_ce", False, "end"), ("tiny_coop_focal", True, "end"),
+                                                 ("tiny_coop_middle", False, "middle"),
+                                                 ("tiny_coop_front", True, "front")])
+def test_coop_step_orchestration_matches_reference_golden(monkeypatch, name, focal, position):
+    """CoOp with every CLASS_TOKEN_POSITION (coop.py:267-293; middle / front = per-class row permutation of the
+    'end' layout) against the unmodified reference's loss, context gradient and context after one SGD step."""
+    TorchKernels().install(monkeypatch)
+    from psrc_b200 import synthetic as S
+    fx = load_golden(name)
+    B, C = fx["label"].shape[0], fx["tokens"].shape[0]
+    alpha = S.focal_alpha(fx["shots"].tolist(), C) if focal else None
+    step, sd = coop_setup("tiny", fx["tokens"], "cpu", "fp32", B, fx["ctx0"], focal_alpha=alpha, position=position)
+    image, label = S.synthetic_batch(B, C, 64, seed=2)
+    assert np.array_equal(label.numpy().astype(np.int32), fx["label"])
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    assert float((step.logits - torch.from_numpy(fx["logits"])).abs().max()) < 1e-4
+    assert abs(float(step.losses.sum()) - float(fx["loss"])) < 2e-5
+    assert cos(step.grads["ctx"], fx["grad/prompt_learner.ctx"]) > 0.99999
+    step.init_optimizer(lr=0.002)
+    step.sgd()
+    assert float((step.params["ctx"] - torch.from_numpy(fx["after/prompt_learner.ctx"])).abs().max()) < 1e-6
 
 
 @pytest.mark.parametrize("name,focal", [("tiny_cocoop_ce", False), ("tiny_cocoop_focal", True)])

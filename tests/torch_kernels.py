@@ -55,7 +55,7 @@ class TorchKernels:
     NAMES = ("gemm", "gemm_f32_strided", "layernorm_fwd", "layernorm_bwd", "attn_fwd", "attn_bwd", "im2col_patches",
              "assemble_vision_tokens", "assemble_text_prompts", "insert_prompt", "prompt_grad", "gather_ln_fwd",
              "gather_ln_bwd", "l2norm_fwd", "l2norm_bwd", "loss_fwd_bwd", "sgd_step", "cast", "axpy",
-             "small_linear_fwd", "small_linear_bwd", "group_logits_fwd", "group_logits_bwd", "ctx_bias_grad")
+             "small_linear_fwd", "small_linear_bwd", "group_logits_fwd", "group_logits_bwd", "ctx_bias_grad", "permute_rows")
 
     def install(self, monkeypatch):
         from psrc_b200 import ops
@@ -297,3 +297,12 @@ class TorchKernels:
     def ctx_bias_grad(gg, dctx, dbias):
         dctx.copy_(gg.sum(0))
         dbias.copy_(gg.sum(1))
+
+    @staticmethod
+    def permute_rows(src, perm, dst, n_seq, L, D, add=None, inverse=False):
+        idx = (torch.arange(n_seq)[:, None] * L + perm.long()).reshape(-1)
+        if inverse:
+            dst[idx] = src
+        else:
+            dst.copy_(src[idx] + (add[:L].repeat(n_seq, 1) if add is not None else 0))
+        return dst
