@@ -40,6 +40,8 @@ def parse_args():
     ap.add_argument("--prec", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--overlap-zs", type=int, default=1,
+                    help="bit 0: frozen tower forward on a second stream (default on); bit 1: text backward on a second stream")
     ap.add_argument("--graph-multi", action="store_true", help="multi-GPU: capture the step incl. NCCL (experimental)")
     ap.add_argument("--no-truncate", action="store_true", help="run all 77 text positions (dense-equivalent)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -237,6 +239,8 @@ def b200_arm(args):
             step.params[f"vision.{i}"].copy_(deep[f"visual.transformer.resblocks.{i}.VPT_shallow"])
             step.params[f"text.{i}"].copy_(deep[f"transformer.resblocks.{i}.VPT_shallow"])
     step.init_optimizer(lr=0.0025, momentum=0.9, weight_decay=5e-4)
+    step.overlap_zero_shot = bool(args.overlap_zs & 1)
+    step.overlap_backward = bool(args.overlap_zs & 2)
     del sd
     g = torch.Generator().manual_seed(1 + rank)
     image_host = torch.randn(B, 3, arch.image_resolution, arch.image_resolution, generator=g).pin_memory()
