@@ -28,8 +28,8 @@ int attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float*
 using namespace psrc;
 
 static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
-// bf16 fast mode: tcgen05 for 32 < L <= 256, one-warp mma.sync tile for L <= 16, CUDA-core half-warp kernel for
-// L <= 32, flash-style mma.sync otherwise
+// bf16 fast mode: tcgen05 for 32 < L <= 256, one-warp mma.sync tiles for L <= 32 (one 16 x 16 score tile up to 16,
+// 2 x 2 tiles up to 32), flash-style mma.sync otherwise; backend 4 (CUDA-core half-warp kernel) stays selectable
 static int auto_backend(int L) {
   if (attn_tc_supported(L)) return 3;
   if (attn_small_mma_supported(L)) return 5;
@@ -46,7 +46,7 @@ extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, 
     backend = (dtype == PSRC_BF16 && al16(qkv) && al16(out)) ? auto_backend(L) : 1;
   if (backend == 5) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out) && attn_small_mma_supported(L),
-                   "psrc_attn_fwd: one-tile mma backend needs aligned bf16 and L <= 16 (L=%d)", L);
+                   "psrc_attn_fwd: mma.sync tile backend needs aligned bf16 and L <= 32 (L=%d)", L);
     return attn_fwd_small_mma(qkv, out, lse, n_seq, L, H, causal, as_stream(stream));
   }
   if (backend == 4) {
@@ -77,7 +77,7 @@ extern "C" int psrc_attn_bwd(const void* qkv, const void* out, const void* dout,
     backend = (dtype == PSRC_BF16 && ok16) ? auto_backend(L) : 1;
   if (backend == 5) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16 && attn_small_mma_supported(L),
-                   "psrc_attn_bwd: one-tile mma backend needs aligned bf16 and L <= 16 (L=%d)", L);
+                   "psrc_attn_bwd: mma.sync tile backend needs aligned bf16 and L <= 32 (L=%d)", L);
     return attn_bwd_small_mma(qkv, dout, lse, dqkv, n_seq, L, H, causal, as_stream(stream));
   }
   if (backend == 4) {

@@ -253,9 +253,257 @@ attn_small_mma_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bflo
   unstage_tile(S.v, drow + 2 * D, ld, L, lane);
 }
 
+
+// ------------------------------------------------------------------------------------------- 16 < L <= 32
+// Two 16-row query tiles and two 16-key tiles per problem (class names of 8+ tokens, e.g. real ImageNet prompts).
+// Same building blocks; the score tile of one query tile is 16 x 32 (four n-tiles), P / dS live in a 32 x 32 shared
+// tile, dK / dV accumulate over the query tiles.
+constexpr int kR2 = 32;     // rows per staged matrix
+constexpr int kXLd2 = 40;   // P / dS tile row stride (32 + 8 pad): 80-byte rows, conflict-free ldmatrix
+
+__device__ __forceinline__ void stage_tile32(__nv_bfloat16* tile, const __nv_bfloat16* __restrict__ src, long long ld,
+                                             int L, int lane) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int idx = lane + 32 * i, r = idx >> 3, c = idx & 7;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (r < L) v = __ldg(reinterpret_cast<const uint4*>(src + (long long)r * ld) + c);
+    *reinterpret_cast<uint4*>(tile + r * kLd + c * 8) = v;
+  }
+}
+// rows [row0, row0 + 16) of a staged tile to global rows row0.. (only rows < L)
+__device__ __forceinline__ void unstage_rows16(const __nv_bfloat16* tile16, __nv_bfloat16* __restrict__ dst, long long ld,
+                                               int row0, int L, int lane) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int idx = lane + 32 * i, r = idx >> 3, c = idx & 7;
+    if (row0 + r < L) *(reinterpret_cast<uint4*>(dst + (long long)(row0 + r) * ld) + c) =
+        *reinterpret_cast<const uint4*>(tile16 + r * kLd + c * 8);
+  }
+}
+// C[16 x 8*NT] = A[16 x 64] . B[8*NT x 64]^T  (A, B: pointers to the first row of the operand inside a staged tile)
+template <int NT>
+__device__ __forceinline__ void mma_abt_n(float (&c)[NT][4], const __nv_bfloat16* A, const __nv_bfloat16* B, int lane) {
+  const int arow = (lane & 7) + ((lane >> 3) & 1) * 8, acol = (lane >> 4) * 8;
+  const int brow = lane & 7, bcol = (lane >> 3) * 8;
+#pragma unroll
+  for (int n = 0; n < NT; ++n)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c[n][i] = 0.f;
+#pragma unroll
+  for (int kk = 0; kk < 4; kk += 2) {
+    uint32_t a0[4], a1[4];
+    ldsm4(a0, A + arow * kLd + kk * 16 + acol);
+    ldsm4(a1, A + arow * kLd + (kk + 1) * 16 + acol);
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+      uint32_t b[4];
+      ldsm4(b, B + (8 * n + brow) * kLd + kk * 16 + bcol);
+      mma16816(c[n], a0, b[0], b[1]);
+      mma16816(c[n], a1, b[2], b[3]);
+    }
+  }
+}
+// C[16 x 64] += A[16 x 16] . B[16 x 64]  (B: pointer to the first of the 16 k-rows)
+__device__ __forceinline__ void mma_ab_acc(float (&c)[8][4], const uint32_t (&a)[4], const __nv_bfloat16* B, int lane) {
+  const int brow = (lane & 7) + ((lane >> 3) & 1) * 8, bcol = (lane >> 4) * 8;
+#pragma unroll
+  for (int n = 0; n < 8; n += 2) {
+    uint32_t b[4];
+    ldsm4t(b, B + brow * kLd + n * 8 + bcol);
+    mma16816(c[n], a, b[0], b[1]);
+    mma16816(c[n + 1], a, b[2], b[3]);
+  }
+}
+__device__ __forceinline__ void zero_acc(float (&c)[8][4]) {
+#pragma unroll
+  for (int n = 0; n < 8; ++n)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c[n][i] = 0.f;
+}
+__device__ __forceinline__ float quad_max(float v) {
+  v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 1));
+  return fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 2));
+}
+__device__ __forceinline__ float quad_sum(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  return v + __shfl_xor_sync(0xffffffffu, v, 2);
+}
+
+constexpr int kWarps2 = 4;
+struct FwdSmem2 {
+  __nv_bfloat16 q[kR2 * kLd], k[kR2 * kLd], v[kR2 * kLd];
+};
+
+template <bool kCausal>
+__global__ void __launch_bounds__(kWarps2 * 32)
+attn_small_mma2_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
+                           float* __restrict__ lse, int n_prob, int L, int H) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int pr = blockIdx.x * kWarps2 + warp;
+  if (pr >= n_prob) return;
+  FwdSmem2& S = reinterpret_cast<FwdSmem2*>(smem_raw)[warp];
+  const int seq = pr / H, h = pr % H, D = H * 64;
+  const long long ld = 3LL * D;
+  const __nv_bfloat16* base = qkv + (long long)seq * L * ld + h * 64;
+  stage_tile32(S.q, base, ld, L, lane);
+  stage_tile32(S.k, base + D, ld, L, lane);
+  stage_tile32(S.v, base + 2 * D, ld, L, lane);
+  __syncwarp();
+  const int g = lane >> 2, t = lane & 3;
+  const int n_qt = (L + 15) >> 4;
+#pragma unroll 1
+  for (int qt = 0; qt < n_qt; ++qt) {
+    float s[4][4];
+    mma_abt_n<4>(s, S.q + qt * 16 * kLd, S.k, lane);
+    float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int row = qt * 16 + g + (i >> 1) * 8, col = n * 8 + 2 * t + (i & 1);
+        const bool ok = col < L && (!kCausal || col <= row);
+        s[n][i] = ok ? s[n][i] * (0.125f * kLog2e) : -INFINITY;
+        if (i < 2) m0 = fmaxf(m0, s[n][i]); else m1 = fmaxf(m1, s[n][i]);
+      }
+    m0 = quad_max(m0);
+    m1 = quad_max(m1);
+    float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        s[n][i] = ex2(s[n][i] - ((i < 2) ? m0 : m1));
+        if (i < 2) sum0 += s[n][i]; else sum1 += s[n][i];
+      }
+    sum0 = quad_sum(sum0);
+    sum1 = quad_sum(sum1);
+    float o[8][4];
+    zero_acc(o);
+#pragma unroll
+    for (int kt = 0; kt < 2; ++kt) {
+      const uint32_t p[4] = {pack_bf16(s[2 * kt][0], s[2 * kt][1]), pack_bf16(s[2 * kt][2], s[2 * kt][3]),
+                             pack_bf16(s[2 * kt + 1][0], s[2 * kt + 1][1]), pack_bf16(s[2 * kt + 1][2], s[2 * kt + 1][3])};
+      mma_ab_acc(o, p, S.v + kt * 16 * kLd, lane);
+    }
+    __syncwarp();                       // all lanes have read Q rows of this tile; they become the O staging rows
+    frags_to_tile(S.q + qt * 16 * kLd, o, 1.f / sum0, 1.f / sum1, g, t);
+    if (t == 0) {
+      float* l = lse + ((long long)seq * H + h) * L;
+      const int r0 = qt * 16 + g;
+      if (r0 < L) l[r0] = (m0 + log2f(sum0)) * kLn2;
+      if (r0 + 8 < L) l[r0 + 8] = (m1 + log2f(sum1)) * kLn2;
+    }
+  }
+  __syncwarp();
+  __nv_bfloat16* orow = out + (long long)seq * L * D + h * 64;
+  unstage_rows16(S.q, orow, (long long)D, 0, L, lane);
+  unstage_rows16(S.q + 16 * kLd, orow, (long long)D, 16, L, lane);
+}
+
+struct BwdSmem2 {
+  __nv_bfloat16 q[kR2 * kLd], k[kR2 * kLd], v[kR2 * kLd], d[kR2 * kLd];
+  __nv_bfloat16 p[kR2 * kXLd2], ds[kR2 * kXLd2];
+  __nv_bfloat16 stg[16 * kLd];
+};
+
+template <bool kCausal>
+__global__ void __launch_bounds__(kWarps2 * 32)
+attn_small_mma2_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
+                           const float* __restrict__ lse, __nv_bfloat16* __restrict__ dqkv, int n_prob, int L, int H) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int pr = blockIdx.x * kWarps2 + warp;
+  if (pr >= n_prob) return;
+  BwdSmem2& S = reinterpret_cast<BwdSmem2*>(smem_raw)[warp];
+  const int seq = pr / H, h = pr % H, D = H * 64;
+  const long long ld = 3LL * D;
+  const __nv_bfloat16* base = qkv + (long long)seq * L * ld + h * 64;
+  stage_tile32(S.q, base, ld, L, lane);
+  stage_tile32(S.k, base + D, ld, L, lane);
+  stage_tile32(S.v, base + 2 * D, ld, L, lane);
+  stage_tile32(S.d, dout + (long long)seq * L * D + h * 64, (long long)D, L, lane);
+  const int g = lane >> 2, t = lane & 3;
+  const float* lrow = lse + ((long long)seq * H + h) * L;
+  __nv_bfloat16* drow = dqkv + (long long)seq * L * ld + h * 64;
+  const int n_t = (L + 15) >> 4;          // query tiles = key tiles
+  __syncwarp();
+  // ---- pass 1 (per query tile): P, dS into the shared tiles; dQ
+#pragma unroll 1
+  for (int qt = 0; qt < 2; ++qt) {
+    float s[4][4], dp[4][4];
+    mma_abt_n<4>(s, S.q + qt * 16 * kLd, S.k, lane);
+    mma_abt_n<4>(dp, S.d + qt * 16 * kLd, S.v, lane);
+    const int r0 = qt * 16 + g;
+    const float l0 = (r0 < L) ? lrow[r0] * kLog2e : 0.f, l1 = (r0 + 8 < L) ? lrow[r0 + 8] * kLog2e : 0.f;
+    float del0 = 0.f, del1 = 0.f;
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int row = r0 + (i >> 1) * 8, col = n * 8 + 2 * t + (i & 1);
+        const bool ok = row < L && col < L && (!kCausal || col <= row);
+        s[n][i] = ok ? ex2(s[n][i] * (0.125f * kLog2e) - ((i < 2) ? l0 : l1)) : 0.f;
+        if (i < 2) del0 = fmaf(s[n][i], dp[n][i], del0); else del1 = fmaf(s[n][i], dp[n][i], del1);
+      }
+    del0 = quad_sum(del0);
+    del1 = quad_sum(del1);
+    uint32_t dsf[8];
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+      dsf[2 * n] = pack_bf16(s[n][0] * (dp[n][0] - del0), s[n][1] * (dp[n][1] - del0));
+      dsf[2 * n + 1] = pack_bf16(s[n][2] * (dp[n][2] - del1), s[n][3] * (dp[n][3] - del1));
+      const int c = n * 8 + 2 * t;
+      *reinterpret_cast<uint32_t*>(S.ds + (qt * 16 + g) * kXLd2 + c) = dsf[2 * n];
+      *reinterpret_cast<uint32_t*>(S.ds + (qt * 16 + g + 8) * kXLd2 + c) = dsf[2 * n + 1];
+      *reinterpret_cast<uint32_t*>(S.p + (qt * 16 + g) * kXLd2 + c) = pack_bf16(s[n][0], s[n][1]);
+      *reinterpret_cast<uint32_t*>(S.p + (qt * 16 + g + 8) * kXLd2 + c) = pack_bf16(s[n][2], s[n][3]);
+    }
+    if (qt < n_t) {
+      float acc[8][4];
+      zero_acc(acc);
+#pragma unroll
+      for (int kt = 0; kt < 2; ++kt) {
+        const uint32_t a[4] = {dsf[4 * kt], dsf[4 * kt + 1], dsf[4 * kt + 2], dsf[4 * kt + 3]};
+        mma_ab_acc(acc, a, S.k + kt * 16 * kLd, lane);       // dQ_qt += dS[qt][kt] K_kt
+      }
+      __syncwarp();                                          // previous unstage of the staging tile is complete
+      frags_to_tile(S.stg, acc, 0.125f, 0.125f, g, t);
+      __syncwarp();
+      unstage_rows16(S.stg, drow, ld, qt * 16, L, lane);
+    }
+  }
+  __syncwarp();
+  // ---- pass 2 (per key tile): dV = P^T dO, dK = 0.125 dS^T Q, accumulated over the query tiles
+  const int xr = (lane & 7) + (lane >> 4) * 8, xc = ((lane >> 3) & 1) * 8;
+#pragma unroll 1
+  for (int kt = 0; kt < n_t; ++kt) {
+#pragma unroll 1
+    for (int which = 0; which < 2; ++which) {              // 0: dV (P, dO)   1: dK (dS, Q)
+      const __nv_bfloat16* X = which ? S.ds : S.p;
+      const __nv_bfloat16* Bm = which ? S.q : S.d;
+      float acc[8][4];
+      zero_acc(acc);
+#pragma unroll
+      for (int qt = 0; qt < 2; ++qt) {
+        if (kCausal && qt < kt) continue;                  // P[qt][kt] = 0 above the diagonal
+        uint32_t a[4];
+        ldsm4t(a, X + (qt * 16 + xr) * kXLd2 + kt * 16 + xc);
+        mma_ab_acc(acc, a, Bm + qt * 16 * kLd, lane);
+      }
+      __syncwarp();
+      const float sc = which ? 0.125f : 1.f;
+      frags_to_tile(S.stg, acc, sc, sc, g, t);
+      __syncwarp();
+      unstage_rows16(S.stg, drow + (which ? D : 2 * D), ld, kt * 16, L, lane);
+    }
+  }
+}
+
 }  // namespace asm2
 
-bool attn_small_mma_supported(int L) { return L >= 1 && L <= 16; }
+bool attn_small_mma_supported(int L) { return L >= 1 && L <= 32; }
 
 int attn_fwd_small_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s) {
   using namespace asm2;
@@ -263,6 +511,20 @@ int attn_fwd_small_mma(const void* qkv, void* out, float* lse, int n_seq, int L,
   const int grid = (n_prob + kWarps - 1) / kWarps;
   const __nv_bfloat16* q = reinterpret_cast<const __nv_bfloat16*>(qkv);
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+  if (L > 16) {
+    const int bytes = kWarps2 * (int)sizeof(FwdSmem2);
+    static bool attr2 = false;
+    if (!attr2) {
+      PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma2_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+      PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma2_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+      attr2 = true;
+    }
+    const int grid2 = (n_prob + kWarps2 - 1) / kWarps2;
+    if (causal) attn_small_mma2_fwd_kernel<true><<<grid2, kWarps2 * 32, bytes, s>>>(q, o, lse, n_prob, L, H);
+    else attn_small_mma2_fwd_kernel<false><<<grid2, kWarps2 * 32, bytes, s>>>(q, o, lse, n_prob, L, H);
+    PSRC_CHECK_LAUNCH();
+    return PSRC_OK;
+  }
   if (causal) attn_small_mma_fwd_kernel<true><<<grid, kWarps * 32, 0, s>>>(q, o, lse, n_prob, L, H);
   else attn_small_mma_fwd_kernel<false><<<grid, kWarps * 32, 0, s>>>(q, o, lse, n_prob, L, H);
   PSRC_CHECK_LAUNCH();
@@ -273,6 +535,23 @@ int attn_bwd_small_mma(const void* qkv, const void* dout, const float* lse, void
                        int causal, cudaStream_t s) {
   using namespace asm2;
   const int n_prob = n_seq * H;
+  if (L > 16) {
+    const int bytes2 = kWarps2 * (int)sizeof(BwdSmem2);
+    static bool attr2 = false;
+    if (!attr2) {
+      PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma2_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes2));
+      PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma2_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes2));
+      attr2 = true;
+    }
+    const int grid2 = (n_prob + kWarps2 - 1) / kWarps2;
+    const __nv_bfloat16* q2 = reinterpret_cast<const __nv_bfloat16*>(qkv);
+    const __nv_bfloat16* d2 = reinterpret_cast<const __nv_bfloat16*>(dout);
+    __nv_bfloat16* dq2 = reinterpret_cast<__nv_bfloat16*>(dqkv);
+    if (causal) attn_small_mma2_bwd_kernel<true><<<grid2, kWarps2 * 32, bytes2, s>>>(q2, d2, lse, dq2, n_prob, L, H);
+    else attn_small_mma2_bwd_kernel<false><<<grid2, kWarps2 * 32, bytes2, s>>>(q2, d2, lse, dq2, n_prob, L, H);
+    PSRC_CHECK_LAUNCH();
+    return PSRC_OK;
+  }
   const int grid = (n_prob + kWarps - 1) / kWarps;
   const int bytes = kWarps * (int)sizeof(BwdSmem);
   static bool attr_set = false;

@@ -109,7 +109,8 @@ int psrc_layernorm_bwd(const void* dy, int dy_dtype, const float* x,
  * out [n_seq*L, D]; lse fp32 [n_seq, H, L] (log-sum-exp of the scaled scores).
  * backend: 0 auto, 1 CUDA-core (any dtype), 2 mma.sync tensor-core (bf16), 3 tcgen05/TMEM (bf16, 32 < L <= 256),
  * 4 short-sequence CUDA-core kernel (bf16, L <= 32, one problem per half warp),
- * 5 one-tile mma.sync kernel (bf16, L <= 16: the truncated text tower, one problem per warp). */
+ * 5 mma.sync tile kernel (bf16, L <= 32: the truncated text tower, one problem per warp; one 16x16 score tile up
+ *   to L = 16, 2 x 2 tiles up to 32). */
 int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype,
                   int n_seq, int L, int H, int causal, int backend,
                   psrc_stream_t stream);

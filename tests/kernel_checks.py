@@ -223,7 +223,9 @@ def check_attention(res: Results, backend_name: str):
     dts = [torch.bfloat16] if backend_name in ("mma", "tc", "small", "small_mma") else [torch.float32, torch.bfloat16]
     if backend_name == "small_mma":  # one 16 x 16 score tile per warp: L <= 16
         cases = [(7, 16, 8, True), (4, 9, 2, True), (5, 11, 8, True), (250, 11, 8, True), (2, 1, 2, True),
-                 (3, 16, 3, False), (5, 13, 1, False), (1001, 11, 8, True), (3, 8, 2, True)]
+                 (3, 16, 3, False), (5, 13, 1, False), (1001, 11, 8, True), (3, 8, 2, True),
+                 (3, 32, 8, True), (3, 17, 2, False), (5, 25, 1, True), (130, 24, 8, True), (2, 31, 3, False),
+                 (4, 20, 12, True)]
     if backend_name == "small":  # short-sequence kernel: L <= 32 (two problems per warp up to L = 16)
         cases = [(7, 16, 8, True), (4, 9, 2, True), (5, 11, 8, True), (3, 32, 8, True), (3, 17, 2, False),
                  (250, 11, 8, True), (2, 1, 2, True), (3, 16, 3, False), (5, 25, 1, True)]
