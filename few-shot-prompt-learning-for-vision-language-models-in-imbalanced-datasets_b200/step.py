@@ -103,13 +103,21 @@ class PromptedClipStep:
             assert cfg.n_ctx_vision == 0 and cfg.depth_text == 1 and not cfg.zero_shot_branch and not cfg.ctx_per_class
             self.c0, self.c1 = 0, C
         else:
-            self.c0, self.c1 = shard_range(C, cfg.world_size, cfg.rank)
-            if cfg.world_size > 1:
-                assert C % cfg.world_size == 0, "class count must divide evenly across ranks (pad the class list)"
+            # equal shards of ceil(C / R) classes (the collectives need equal chunks); when C is not a multiple of R the
+            # tail of the last shard(s) is padding: dummy sequences (a copy of the last class) that run through the text
+            # tower but never reach the logits, receive a zero gradient and are excluded from the L1-text term
+            per = -(-C // cfg.world_size)
+            self.c0 = cfg.rank * per
+            self.c1 = self.c0 + per
+            if cfg.world_size > 1 and per * cfg.world_size != C:
+                assert not cfg.ctx_per_class, "class-specific contexts need a class count divisible by the world size"
         if cfg.coupling:
             assert cfg.n_ctx_vision == cfg.n_ctx_text and cfg.depth_vision == cfg.depth_text and not cfg.ctx_per_class, \
                 "MaPLe couples one vision prompt to each text prompt (maple.py:150-156)"
         self.Cl = self.c1 - self.c0
+        self.Cv = max(0, min(C, self.c1) - self.c0)            # real (non-padding) classes of this shard
+        self.C_pad = self.Cl * cfg.world_size if not self.per_image else C
+        cls_idx = torch.arange(self.c0, self.c1).clamp(max=C - 1)
         self.share_text = cfg.world_size > 1 and not self.per_image   # all-gather t_hat / reduce-scatter dt_hat
         self.B_global = B * cfg.world_size
         self.Dv, self.Dt, self.E = a.vision_width, a.transformer_width, a.embed_dim
@@ -136,10 +144,10 @@ class PromptedClipStep:
         assert tokens.shape[0] == C
         eot_all = tokens.argmax(-1)                                          # promptsrc.py:68
         self.Lt = int(eot_all.max()) + 1 if cfg.truncate_text else a.context_length
-        emb = clip_sd["token_embedding.weight"][tokens[self.c0:self.c1]]     # promptsrc.py:121
+        emb = clip_sd["token_embedding.weight"][tokens[cls_idx]]             # promptsrc.py:121
         self.token_prefix = _dev(emb[:, :1], dev)                           # promptsrc.py:136
         self.token_suffix = _dev(emb[:, 1 + cfg.n_ctx_text:], dev)          # promptsrc.py:137
-        self.eot = eot_all[self.c0:self.c1].to(torch.int32).to(dev)
+        self.eot = eot_all[cls_idx].to(torch.int32).to(dev)
         # CoOp class-token positions other than "end": the prompt is the "end" layout with its rows permuted per class
         self.text_perm = None
         if cfg.class_token_position != "end":
@@ -147,7 +155,7 @@ class PromptedClipStep:
             assert cfg.depth_text == 1 and not self.per_image, "class-token positions are a CoOp option (coop.py:267)"
             perm = torch.arange(self.Lt, dtype=torch.int32).repeat(self.Cl, 1)
             n_c = cfg.n_ctx_text
-            for i, e_ in enumerate(eot_all[self.c0:self.c1].tolist()):
+            for i, e_ in enumerate(eot_all[cls_idx].tolist()):
                 name_len = e_ - n_c - 2                                      # SOT, ctx, name tokens, ".", EOT
                 assert name_len >= 0
                 ctx_pos = list(range(1, 1 + n_c))
@@ -180,11 +188,12 @@ class PromptedClipStep:
         self.hv_stats, self.ht_stats = (e(B), e(B)), (e(Ts), e(Ts))
         self.f, self.f_hat, self.f_inv = e(B, self.E), e(B, self.E), e(B)
         self.t, self.t_hat_l, self.t_inv = e(Ts, self.E), e(Ts, self.E), e(Ts)
-        self.t_hat = e(C, self.E) if self.share_text else self.t_hat_l
+        self.t_hat = e(self.C_pad, self.E) if self.share_text else self.t_hat_l
         self.logits, self.d_logits = e(B, C), e(B, C)
         self.d_fhat, self.d_that_l = e(B, self.E), e(Ts, self.E)
-        self.d_that_full = e(C, self.E) if self.share_text else None
-        self.d_that_l1 = e(self.Cl, self.E) if self.share_text else None
+        # zero-initialised: the rows of padding classes are never written and must stay zero
+        self.d_that_full = torch.zeros(self.C_pad, self.E, device=dev) if self.share_text else None
+        self.d_that_l1 = torch.zeros(self.Cl, self.E, device=dev) if self.share_text else None
         self.df, self.dt_ = e(B, self.E), e(Ts, self.E)
         self.df_a = e(B, self.E, dt=self.act) if self.act != torch.float32 else self.df
         self.dt_a = e(Ts, self.E, dt=self.act) if self.act != torch.float32 else self.dt_
@@ -213,7 +222,8 @@ class PromptedClipStep:
             self.fixed_hat = e(C, self.E)
             ops.l2norm_fwd(fe, self.fixed_hat, None)                          # promptsrc.py:196-197
             self.fixed_hat_h = self.fixed_hat.to(torch.float16).to(torch.float32)  # `.half()` at :201 (init-time)
-            self.fixed_hat_l = self.fixed_hat[self.c0:self.c1].contiguous()
+            self.fixed_hat_l = torch.zeros(self.Cl, self.E, device=dev)
+            self.fixed_hat_l[:self.Cv].copy_(self.fixed_hat[self.c0:self.c0 + self.Cv])
 
         # ---- trainable prompt parameters live in ONE flat fp32 buffer (+ flat grad buffer)
         self.param_shapes = {}
@@ -423,8 +433,9 @@ class PromptedClipStep:
         ops.loss_fwd_bwd(self.logits, self.labels, self.d_logits, self.losses, self.loss_scratch,
                          zs_logits=self.zs_logits if zs else None, focal_alpha=self.focal_alpha,
                          focal_gamma=cfg.focal_gamma,
-                         t_hat=self.t_hat_l if zs else None, t_zs=self.fixed_hat_l if zs else None,
-                         d_that=d_that_l1 if zs else None,
+                         t_hat=self.t_hat_l[:self.Cv] if (zs and self.Cv) else None,
+                         t_zs=self.fixed_hat_l[:self.Cv] if (zs and self.Cv) else None,
+                         d_that=d_that_l1[:self.Cv] if (zs and self.Cv) else None,
                          f_hat=self.f_hat if zs else None, f_zs=self.zf_hat if zs else None,
                          d_fhat=self.d_fhat if zs else None,
                          w_kl=cfg.w_logits, w_text=cfg.w_text, w_image=cfg.w_image,
@@ -472,7 +483,7 @@ class PromptedClipStep:
             assert not zs
             ops.group_logits_bwd(self.f_hat, self.d_logits, self.d_that_l, self.scale)
         elif self.share_text:
-            ops.gemm_f32_strided(C, E, B, self.d_logits, 1, C, self.f_hat, 1, E, self.d_that_full, alpha=self.scale)
+            ops.gemm_f32_strided(C, E, B, self.d_logits, 1, C, self.f_hat, 1, E, self.d_that_full[:C], alpha=self.scale)
             dist.reduce_scatter_tensor(self.d_that_l, self.d_that_full, group=cfg.process_group)
             if zs:
                 ops.axpy(self.d_that_l, self.d_that_l1, 1.0)
@@ -507,7 +518,7 @@ class PromptedClipStep:
         elif cfg.ctx_per_class:
             g = self.grads["ctx"]
             g.zero_()
-            g[self.c0:self.c1].copy_(dx0.view(self.Cl, self.Lt, self.Dt)[:, 1:1 + cfg.n_ctx_text])
+            g[self.c0:self.c0 + self.Cv].copy_(dx0.view(self.Cl, self.Lt, self.Dt)[:self.Cv, 1:1 + cfg.n_ctx_text])
         else:
             ops.prompt_grad(dx0, self.grads["ctx"], self.Cl, self.Lt, 1, cfg.n_ctx_text, self.Dt,
                             zero_rows=False, round_fp16=False)               # ctx has no .half() (promptsrc.py:160)

@@ -446,7 +446,8 @@ def _focal_alpha_from_cfg(cfg, n_cls):
 class PromptSRCCustomCLIP(_CustomCLIPBase):
     """CustomCLIP of trainers/promptsrc.py:170-213.  Extra keyword arguments (all optional) exist because the
     reference obtains them from the network / its tokenizer: `tokenized_prompts` int64 [C, 77],
-    `teacher_tokens` (the "a photo of a {}." prompts, promptsrc.py:124-129), `fixed_embeddings`."""
+    `teacher_tokens` (the "a photo of a {}." prompts, promptsrc.py:124-129; or `[T, C, 77]` for the template-ensemble
+    teacher of promptsrc_pets_focal.py:165-175), `fixed_embeddings`."""
 
     def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, teacher_tokens=None,
                  fixed_embeddings=None, device=None):
@@ -475,7 +476,13 @@ class PromptSRCCustomCLIP(_CustomCLIPBase):
                 same = (ctx_init or "").strip().lower() == "a photo of a"
                 teacher_tokens = tokens if same else _reference_tokenize([f"a photo of a {n}." for n in names])
             sd = {k: v.detach().float().cpu() for k, v in clip_model.state_dict().items()}
-            fixed_embeddings = encode_text_frozen(sd, torch.as_tensor(teacher_tokens).long(), dev, prec="fp32")
+            tt_ = torch.as_tensor(teacher_tokens).long()
+            if tt_.dim() == 3:
+                # template ensemble of the teacher (promptsrc_pets_focal.py:165-175: one encode_text pass per template,
+                # mean of the un-normalised features over templates); teacher_tokens is [T, C, 77]
+                fixed_embeddings = torch.stack([encode_text_frozen(sd, t_, dev, prec="fp32") for t_ in tt_]).mean(0)
+            else:
+                fixed_embeddings = encode_text_frozen(sd, tt_, dev, prec="fp32")
         depth_v = int(T.PROMPT_DEPTH_VISION)
         kw = dict(prec_cfg=T.PREC, n_ctx_text=n_ctx, n_ctx_vision=int(T.N_CTX_VISION) if depth_v >= 1 else 0,
                   depth_text=int(T.PROMPT_DEPTH_TEXT), depth_vision=depth_v, zero_shot_branch=True,

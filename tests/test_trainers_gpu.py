@@ -79,3 +79,9 @@ def test_maple_cocoop_bf16_mode_runs():
     for fn in (TC.check_maple, TC.check_cocoop):
         m = fn("fp16")
         assert max(m["loss_abs_0"], m["loss_abs_1"], m["loss_abs_2"]) < 5e-2, m
+
+
+def test_frozen_teacher_precompute_single_and_ensemble():
+    _need_gpu()
+    m = TC.check_teacher_ensemble()
+    assert m["ensemble_rel"] < 2e-5 and m["single_rel"] < 2e-5, m

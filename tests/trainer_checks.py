@@ -287,6 +287,27 @@ def check_cocoop(prec="fp32", focal=False):
     return m
 
 
+def check_teacher_ensemble():
+    """Frozen-teacher precompute through the kernels: single template and a 3-template ensemble
+    (promptsrc_pets_focal.py:165-175) against the oracle's frozen text tower."""
+    import clip_oracle as O
+    from psrc_b200 import synthetic as S, trainers as T
+    arch = S.ARCHS["tiny"]
+    sd = S.make_clip_state_dict(arch, seed=0)
+    lens = [[1, 2, 3, 8, 1, 1, 2, 2, 1, 2], [2, 2, 3, 5, 1, 4, 2, 2, 1, 2], [1, 1, 1, 9, 3, 1, 2, 6, 1, 2]]
+    templ = torch.stack([torch.as_tensor(S.synthetic_tokens(10, name_lens=nl, seed=7 + i)) for i, nl in enumerate(lens)])
+    ref = torch.stack([O.teacher_text_features(sd, t_, arch.transformer_heads) for t_ in templ]).mean(0)
+    cfg = trainer_cfg("PromptSRC", batch=B, depth=DEPTH, prec="fp32")
+    clip_model = T.synthetic_clip("tiny", 0, N_CTX, N_CTX, DEPTH, DEPTH)
+    model = T.PromptSRCCustomCLIP(cfg, [f"c{i}" for i in range(10)], clip_model, tokenized_prompts=templ[0],
+                                  teacher_tokens=templ, device="cuda")
+    got = model.prompt_learner.fixed_embeddings.cpu()
+    single = T.PromptSRCCustomCLIP(cfg, [f"c{i}" for i in range(10)], clip_model, tokenized_prompts=templ[0],
+                                   teacher_tokens=templ[0], device="cuda").prompt_learner.fixed_embeddings.cpu()
+    ref1 = O.teacher_text_features(sd, templ[0], arch.transformer_heads)
+    return {"ensemble_rel": float((got - ref).norm() / ref.norm()), "single_rel": float((single - ref1).norm() / ref1.norm())}
+
+
 def check_coop(prec="fp32", loss_type="ce"):
     import clip_oracle as O
     from psrc_b200 import synthetic as S
