@@ -13,6 +13,7 @@
 // Reference: nn.MultiheadAttention core called from PromptSRC/clip/model.py:183/227/285, causal mask
 // model.py:592-598.
 #include <cuda.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace psrc {
@@ -610,6 +611,261 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
   if (warp == 8) tmem_dealloc(tb, 512);
 }
 
+// ------------------------------------------------------------------------------------------- backward, pipelined
+// Same mathematics and orientations as attn_bwd_tc_kernel, one CTA per (sequence, head), but the columns of every
+// 128-lane phase are walked in chunks of <= 64 through TWO TMEM chunk buffers (S_c | dP_c, 128 columns each) and two
+// output buffers (out A | out B), so that the MMA warp computes the scores of chunk i+1 and the output products of
+// chunk i-1 while the eight elementwise warps -- which are bound by the 64 B/clk TMEM read port -- work on chunk i,
+// and the epilogue of a phase is deferred until after the first chunk of the next one.  tcgen05.mma issue order
+// keeps chunk i-1's output MMAs (A = packed dS / P inside the chunk buffer) ahead of chunk i+1's score MMAs that
+// overwrite the same buffer.
+constexpr uint32_t kP3Buf = 128, kP3DP = 64, kP3Out = 256, kP3OutB = 64;
+constexpr int kBwd3Threads = 320;   // warps 0-7 elementwise + epilogue, warp 8: TMEM / TMA / MMA issuer A, warp 9: MMA issuer B
+#ifdef PSRC_ATTN_TIMELINE   // dev instrumentation (tests/attn_timeline.cu): clock64 stamps of one (sequence, head)
+__device__ long long g_tl[2][64];
+#define TL(who, idx) do { if (blockIdx.y == gridDim.y / 2 && blockIdx.x == 3) g_tl[who][idx] = clock64(); } while (0)
+#else
+#define TL(who, idx) do { } while (0)
+#endif
+
+template <bool kCausal>
+__global__ void __launch_bounds__(kBwd3Threads)
+attn_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
+                    const __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ dout,
+                    const float* __restrict__ lse, __nv_bfloat16* __restrict__ dqkv, int L, int H, float scale,
+                    float scale_log2) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int n_mt = (L + 127) >> 7;
+  const int n_phase = 2 * n_mt;
+  const int Lp = (L + 15) & ~15;
+  const int n_grp = Lp >> 4;                      // 16-column groups
+  const int n_ch = (n_grp + 3) >> 2;              // chunks of at most 4 groups, sizes as even as possible
+  const int g_base = n_grp / n_ch, g_rem = n_grp % n_ch;
+  const int n_step = n_phase * n_ch;
+  uint8_t* Qs = smem;
+  uint8_t* Ks = Qs + n_mt * kTile;
+  uint8_t* Vs = Ks + n_mt * kTile;
+  uint8_t* dOs = Vs + n_mt * kTile;
+  float* lse2_s = reinterpret_cast<float*>(dOs + n_mt * kTile);
+  float* delta_s = lse2_s + 256;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(delta_s + 256);
+  uint64_t *bar_load = bars, *bar_s = bars + 1, *bar_p = bars + 3, *bar_o = bars + 5, *bar_e = bars + 7;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 9);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = blockIdx.x, seq = blockIdx.y;
+  const int D = H * 64;
+  const long long ld3 = 3LL * D;
+
+  if (warp == 8) {
+    if (lane == 0) {
+      TL(0, 0);
+      tma_prefetch_desc(&tmap_qkv);
+      tma_prefetch_desc(&tmap_do);
+      mbar_init(bar_load, 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(bar_s + i, 2);   // one tcgen05.commit from each of the two issuing threads
+        mbar_init(bar_p + i, 8);
+        mbar_init(bar_o + i, 2);
+        mbar_init(bar_e + i, 8);
+      }
+      fence_mbar_init();
+      mbar_expect_tx(bar_load, 4 * n_mt * kTile);   // the loads do not depend on the TMEM allocation
+      for (int t = 0; t < n_mt; ++t) {
+        tma_load_3d(&tmap_qkv, bar_load, Qs + t * kTile, h * 64, t * 128, seq);
+        tma_load_3d(&tmap_qkv, bar_load, Ks + t * kTile, D + h * 64, t * 128, seq);
+        tma_load_3d(&tmap_do, bar_load, dOs + t * kTile, h * 64, t * 128, seq);
+        tma_load_3d(&tmap_qkv, bar_load, Vs + t * kTile, 2 * D + h * 64, t * 128, seq);
+      }
+    }
+    __syncwarp();
+    tmem_alloc(tslot, 512);
+    tmem_relinquish();
+  }
+  // ---- prologue, part 1: the global loads behind delta_i = <dO_i, O_i> need neither TMEM nor the barriers -- they are
+  //      issued before the CTA-wide sync and consumed after it
+  uint4 pro_a[8], pro_b[8];
+  float pro_l2 = 1e30f;              // padding rows: exp2(s - 1e30) = 0
+  const int pro_i = warp * 32 + lane;
+  if (warp < 8 && pro_i < L) {
+    const uint4* po = reinterpret_cast<const uint4*>(out + ((long long)seq * L + pro_i) * D + h * 64);
+    const uint4* pd = reinterpret_cast<const uint4*>(dout + ((long long)seq * L + pro_i) * D + h * 64);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) { pro_a[c] = po[c]; pro_b[c] = pd[c]; }
+    pro_l2 = lse[((long long)seq * H + h) * L + pro_i] * kLog2e;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tb = *tslot;
+
+  if (warp >= 8) {
+    // Two issuing threads (warp 8: everything that touches the S half of a chunk buffer -- score MMAs and the output
+    // MMAs whose A operand is packed there (dQ / dV); warp 9: the dP half -- dP MMAs and dK).  Measured: one thread
+    // issues a narrow tcgen05.mma every ~100-200 clk, far above the tensor-pipe floor (32 clk at N = 64), so a single
+    // issuer was the bottleneck of the pipelined loop.  Each thread's own issue order covers its write-after-read
+    // hazards (the next scores overwrite the columns its previous output MMAs read).
+    if (lane == 0) {
+      const bool second = warp == 9;
+      if (!second) TL(0, 1);
+      wait_bounded(bar_load, 0);
+      if (!second) TL(0, 2);
+      const uint32_t qs = smem_u32(Qs), ks = smem_u32(Ks), vs = smem_u32(Vs), ds = smem_u32(dOs);
+      auto issue_sd = [&](int ph, int c, int b) {
+        const bool ql = ph < n_mt;
+        const int t = ql ? ph : ph - n_mt;
+        const int ng = g_base + (c < g_rem ? 1 : 0);
+        const uint32_t roff = (uint32_t)(c * g_base + min(c, g_rem)) * 2048;   // 16 rows x 128 B per group
+        const uint32_t idesc = idesc_kk(ng * 16);
+        const uint32_t a_op = (second ? (ql ? ds : vs) : (ql ? qs : ks)) + t * kTile;
+        const uint32_t b_op = (second ? (ql ? vs : ds) : (ql ? ks : qs)) + roff;
+        const uint32_t tS = tb + (uint32_t)b * kP3Buf + (second ? kP3DP : 0u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_bf16(tS, desc_kmajor(a_op + k * 32), desc_kmajor(b_op + k * 32), idesc, k > 0);
+        umma_commit(bar_s + b);
+      };
+      issue_sd(0, 0, 0);
+      int ph = 0, c = 0;          // current step
+      int ph_n = 0, c_n = 0;      // next step
+      for (int i = 0; i < n_step; ++i) {
+        if (++c_n == n_ch) { c_n = 0; ++ph_n; }
+        if (i + 1 < n_step) issue_sd(ph_n, c_n, (i + 1) & 1);
+        if (!second) TL(0, 22 + i);
+        wait_bounded(bar_p + (i & 1), (i >> 1) & 1);
+        tc_fence_after();
+        if (!second) TL(0, 3 + i);
+        if (c == 0 && ph >= 2) {   // output buffer ph & 1 was last read by the epilogue of phase ph - 2
+          wait_bounded(bar_e + (ph & 1), ((ph - 2) >> 1) & 1);
+          tc_fence_after();
+        }
+        const bool ql = ph < n_mt;
+        const int ng = g_base + (c < g_rem ? 1 : 0);
+        const uint32_t roff = (uint32_t)(c * g_base + min(c, g_rem)) * 2048;
+        const uint32_t tS = tb + (uint32_t)(i & 1) * kP3Buf;
+        const uint32_t tO = tb + kP3Out + (uint32_t)(ph & 1) * 128;
+        if (!second) {
+          const uint32_t bop = (ql ? ks : ds) + roff;            // dQ += dS K   |   dV += P^T dO
+          for (int k = 0; k < ng; ++k)
+            umma_bf16_ts(tO, tS + (uint32_t)((k >> 1) * 32 + (k & 1) * 8), desc_mnmajor(bop + k * 2048), kIdescMn64,
+                         (c > 0 || k > 0) ? 1u : 0u);
+        } else if (!ql) {
+          for (int k = 0; k < ng; ++k)                             // dK += dS^T Q
+            umma_bf16_ts(tO + kP3OutB, tS + kP3DP + (uint32_t)((k >> 1) * 32 + (k & 1) * 8),
+                         desc_mnmajor(qs + roff + k * 2048), kIdescMn64, (c > 0 || k > 0) ? 1u : 0u);
+        }
+        if (c == n_ch - 1) umma_commit(bar_o + (ph & 1));
+        if (!second) TL(0, 40 + i);
+        if (++c == n_ch) { c = 0; ++ph; }
+      }
+      if (!second) TL(0, 20);
+    }
+  } else {
+    const int q = warp & 3, hh = warp >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t tl = tb + ((uint32_t)(q * 32) << 16);
+    {  // prologue, part 2
+      float acc = 0.f;
+      if (pro_i < L) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&pro_a[c]);
+          const __nv_bfloat162* hb = reinterpret_cast<const __nv_bfloat162*>(&pro_b[c]);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 fa = __bfloat1622float2(ha[j]), fb = __bfloat1622float2(hb[j]);
+            acc = fmaf(fa.x, fb.x, acc);
+            acc = fmaf(fa.y, fb.y, acc);
+          }
+        }
+      }
+      delta_s[pro_i] = acc;
+      lse2_s[pro_i] = pro_l2;
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");  // the eight elementwise warps only
+    if (threadIdx.x == 0) TL(1, 0);
+
+    // accumulators of phase p -> registers -> global; the TMEM buffer is handed back before the stores
+    auto epilogue = [&](int p) {
+      const bool ql = p < n_mt;
+      const int row = (ql ? p : p - n_mt) * 128 + r;
+      wait_bounded(bar_o + (p & 1), (p >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tO = tl + kP3Out + (uint32_t)(p & 1) * 128;
+      __nv_bfloat16* drow = dqkv + ((long long)seq * L + row) * ld3 + h * 64;
+      if (ql) {  // dQ: each warp of the pair writes 32 of the 64 dims
+        uint32_t a[32];
+        tmem_ld_32x32(tO + hh * 32, a);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_e + (p & 1));
+        if (row < L) store_row32(drow + hh * 32, a, scale);
+      } else {   // hh = 0: dV, hh = 1: dK (scaled)
+        uint32_t a[32], b[32];
+        const uint32_t col = hh ? kP3OutB : 0;
+        tmem_ld_32x32(tO + col, a);
+        tmem_ld_32x32(tO + col + 32, b);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_e + (p & 1));
+        if (row < L) store_row64(drow + (hh ? D : 2 * D), a, b, hh ? scale : 1.f);
+      }
+      if (threadIdx.x == 0) TL(1, 40 + p);
+    };
+
+    int ph = 0, c = 0;
+    for (int i = 0; i < n_step; ++i) {
+      const bool ql = ph < n_mt;
+      const int row = (ql ? ph : ph - n_mt) * 128 + r;
+      const int ng = g_base + (c < g_rem ? 1 : 0);
+      const int wc = ng * 16;
+      const int loc = hh * 32;                       // this warp's first column inside the chunk
+      const float l2r = lse2_s[row < 256 ? row : 0], dlr = delta_s[row < 256 ? row : 0];
+      wait_bounded(bar_s + (i & 1), (i >> 1) & 1);
+      tc_fence_after();
+      if (threadIdx.x == 0) TL(1, 1 + 2 * i);
+      if (loc < wc) {
+        const int c0 = (c * g_base + min(c, g_rem)) * 16 + loc;   // logical column (key or query index)
+        const bool wide = loc + 32 <= wc;
+        const bool straddles = c0 + (wide ? 32 : 16) > L;
+        // bwd_chunk addresses TMEM as base + c0 (fp32) and base + c0/2 (packed): bias the bases to buffer-local columns
+        const uint32_t tbuf = tl + (uint32_t)(i & 1) * kP3Buf + (uint32_t)loc;
+        const uint32_t t_s = tbuf - (uint32_t)c0, t_dp = tbuf + kP3DP - (uint32_t)c0;
+        const uint32_t t_ps = tbuf - (uint32_t)(c0 >> 1), t_dk = tbuf + kP3DP - (uint32_t)(c0 >> 1);
+        if (ql) {
+          if (wide) {
+            if (straddles) bwd_chunk<32, false, kCausal, true>(t_s, t_dp, t_ps, t_ps, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+            else bwd_chunk<32, false, kCausal, false>(t_s, t_dp, t_ps, t_ps, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+          } else {
+            if (straddles) bwd_chunk<16, false, kCausal, true>(t_s, t_dp, t_ps, t_ps, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+            else bwd_chunk<16, false, kCausal, false>(t_s, t_dp, t_ps, t_ps, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+          }
+        } else {
+          if (wide)
+            bwd_chunk<32, true, kCausal, false>(t_s, t_dp, t_ps, t_dk, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+          else
+            bwd_chunk<16, true, kCausal, false>(t_s, t_dp, t_ps, t_dk, c0, row, L, scale_log2, l2r, dlr, lse2_s, delta_s);
+        }
+        tmem_st_wait();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_p + (i & 1));
+      if (threadIdx.x == 0) TL(1, 2 + 2 * i);
+      if (c == 0 && ph > 0) epilogue(ph - 1);       // deferred: the next phase's first chunk is already with the MMA warp
+      if (++c == n_ch) { c = 0; ++ph; }
+    }
+    epilogue(n_phase - 1);
+    if (threadIdx.x == 0) TL(1, 50);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 8) tmem_dealloc(tb, 512);
+}
+
 // ---------------------------------------------------------------------------- host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
@@ -685,16 +941,33 @@ int attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float*
                 int H, int causal, cudaStream_t s) {
   using namespace atc;
   const int n_mt = (L + 127) >> 7;
-  const size_t smem = (size_t)4 * n_mt * kTile + 2 * 256 * sizeof(float) + 64 + 1024;
   CUtensorMap map_qkv, map_do;
   int rc = make_map3(&map_qkv, qkv, n_seq, L, 3LL * H * 64);
   if (rc) return rc;
   if ((rc = make_map3(&map_do, dout, n_seq, L, (long long)H * 64))) return rc;
-  dim3 grid(H, n_seq);
   const float scale = 0.125f, scale_log2 = 0.125f * kLog2e;
   const __nv_bfloat16* o = reinterpret_cast<const __nv_bfloat16*>(out);
   const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(dout);
   __nv_bfloat16* dq = reinterpret_cast<__nv_bfloat16*>(dqkv);
+  // PSRC_ATTN_BWD = 1: serial kernel; 3: chunk-pipelined kernel; unset: by shape
+  static const int version = getenv("PSRC_ATTN_BWD") ? atoi(getenv("PSRC_ATTN_BWD")) : 0;
+  // measured on B200 (tests/attn_bench.py): L = 201: 249 vs 255 us, L = 77 causal: 478 vs 467 us -> pipelined kernel
+  // when there are two lane tiles (16 steps to pipeline), serial kernel otherwise
+  if (version == 3 || (version == 0 && n_mt >= 2)) {
+    const size_t smem3 = (size_t)4 * n_mt * kTile + 2 * 256 * sizeof(float) + 128 + 1024;
+    dim3 grid3(H, n_seq);
+    if (causal) {
+      if ((rc = set_smem(attn_bwd_tc3_kernel<true>, smem3))) return rc;
+      attn_bwd_tc3_kernel<true><<<grid3, kBwd3Threads, smem3, s>>>(map_qkv, map_do, o, d, lse, dq, L, H, scale, scale_log2);
+    } else {
+      if ((rc = set_smem(attn_bwd_tc3_kernel<false>, smem3))) return rc;
+      attn_bwd_tc3_kernel<false><<<grid3, kBwd3Threads, smem3, s>>>(map_qkv, map_do, o, d, lse, dq, L, H, scale, scale_log2);
+    }
+    PSRC_CHECK_LAUNCH();
+    return PSRC_OK;
+  }
+  const size_t smem = (size_t)4 * n_mt * kTile + 2 * 256 * sizeof(float) + 64 + 1024;
+  dim3 grid(H, n_seq);
   if (causal) {
     if ((rc = set_smem(attn_bwd_tc_kernel<true>, smem))) return rc;
     attn_bwd_tc_kernel<true><<<grid, kBwdThreads, smem, s>>>(map_qkv, map_do, o, d, lse, dq, L, H, scale, scale_log2);
