@@ -60,57 +60,78 @@ gemm_simt_kernel(const T* __restrict__ A, long long lda, const T* __restrict__ W
   }
 }
 
+// C[M,N] = alpha * A . B^T + beta * C with arbitrary element strides.  T x T block tile (T = 64: 4x4 per thread, T = 32:
+// 2x2 -- the logit contractions are 128 x 1000 x 512 and smaller, so the small tile is what fills the SMs), 16-deep
+// k-tiles, the next k-tile's global loads in flight (registers) while the current one is multiplied.
+template <int T>
 __global__ void __launch_bounds__(256)
 gemm_f32_strided_kernel(int M, int N, int K, const float* __restrict__ A, long long a_sm, long long a_sk,
                         const float* __restrict__ B, long long b_sn, long long b_sk, float* __restrict__ C,
                         long long ldc, float alpha, float beta) {
-  __shared__ float sA[kTK][kTM + 4];
-  __shared__ float sB[kTK][kTN + 4];
+  constexpr int MT = T / 16;             // micro-tile edge
+  constexpr int NL = T * kTK / 256;      // elements of each operand tile loaded per thread
+  __shared__ float sA[kTK][T + 4];
+  __shared__ float sB[kTK][T + 4];
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
-  const int m0 = blockIdx.y * kTM, n0 = blockIdx.x * kTN;
-  float acc[4][4];
+  const int m0 = blockIdx.y * T, n0 = blockIdx.x * T;
+  float acc[MT][MT];
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < MT; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < MT; ++j) acc[i][j] = 0.f;
   // Two load mappings so that the contiguous global dimension maps to consecutive threads.
   const bool a_kfast = (a_sk == 1), b_kfast = (b_sk == 1);
+  float ra[NL], rb[NL];
+  auto fetch = [&](int k0) {
+#pragma unroll
+    for (int i = 0; i < NL; ++i) {
+      const int e = tid + i * 256;  // over a T x 16 tile
+      int r, k;
+      if (a_kfast) { r = e >> 4; k = e & 15; } else { r = e % T; k = e / T; }
+      const int m = m0 + r;
+      int kk = k0 + k;
+      ra[i] = (m < M && kk < K) ? A[(long long)m * a_sm + (long long)kk * a_sk] : 0.f;
+      if (b_kfast) { r = e >> 4; k = e & 15; } else { r = e % T; k = e / T; }
+      const int n = n0 + r;
+      kk = k0 + k;
+      rb[i] = (n < N && kk < K) ? B[(long long)n * b_sn + (long long)kk * b_sk] : 0.f;
+    }
+  };
+  fetch(0);
   for (int k0 = 0; k0 < K; k0 += kTK) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      int e = tid + i * 256;  // 0..1023 over a 64 x 16 tile
+    for (int i = 0; i < NL; ++i) {
+      const int e = tid + i * 256;
       int r, k;
-      if (a_kfast) { r = e >> 4; k = e & 15; } else { r = e & 63; k = e >> 6; }
-      int m = m0 + r, kk = k0 + k;
-      sA[k][r] = (m < M && kk < K) ? A[(long long)m * a_sm + (long long)kk * a_sk] : 0.f;
-      if (b_kfast) { r = e >> 4; k = e & 15; } else { r = e & 63; k = e >> 6; }
-      int n = n0 + r;
-      kk = k0 + k;
-      sB[k][r] = (n < N && kk < K) ? B[(long long)n * b_sn + (long long)kk * b_sk] : 0.f;
+      if (a_kfast) { r = e >> 4; k = e & 15; } else { r = e % T; k = e / T; }
+      sA[k][r] = ra[i];
+      if (b_kfast) { r = e >> 4; k = e & 15; } else { r = e % T; k = e / T; }
+      sB[k][r] = rb[i];
     }
     __syncthreads();
+    if (k0 + kTK < K) fetch(k0 + kTK);
 #pragma unroll
     for (int k = 0; k < kTK; ++k) {
-      float a[4], b[4];
+      float a[MT], b[MT];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) a[i] = sA[k][ty * 4 + i];
+      for (int i = 0; i < MT; ++i) a[i] = sA[k][ty * MT + i];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) b[j] = sB[k][tx * 4 + j];
+      for (int j = 0; j < MT; ++j) b[j] = sB[k][tx * MT + j];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < MT; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        for (int j = 0; j < MT; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
     }
     __syncthreads();
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    int m = m0 + ty * 4 + i;
+  for (int i = 0; i < MT; ++i) {
+    const int m = m0 + ty * MT + i;
     if (m >= M) continue;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      int n = n0 + tx * 4 + j;
+    for (int j = 0; j < MT; ++j) {
+      const int n = n0 + tx * MT + j;
       if (n >= N) continue;
       float* c = C + (long long)m * ldc + n;
       float v = alpha * acc[i][j];
@@ -167,9 +188,16 @@ extern "C" int psrc_gemm_f32_strided(int M, int N, int K, const float* A, int64_
                                      float alpha, float beta, psrc_stream_t stream) {
   PSRC_CHECK_ARG(M >= 0 && N >= 0 && K > 0 && A && B && C, "psrc_gemm_f32_strided: bad arguments");
   if (M == 0 || N == 0) return PSRC_OK;
-  dim3 grid((N + kTN - 1) / kTN, (M + kTM - 1) / kTM);
-  gemm_f32_strided_kernel<<<grid, 256, 0, as_stream(stream)>>>(M, N, K, A, a_sm, a_sk, B, b_sn, b_sk, C, ldc,
-                                                               alpha, beta);
+  // 64 x 64 tiles only when they alone give every SM a block
+  if ((long long)((N + 63) / 64) * ((M + 63) / 64) >= 148) {
+    dim3 grid((N + 63) / 64, (M + 63) / 64);
+    gemm_f32_strided_kernel<64><<<grid, 256, 0, as_stream(stream)>>>(M, N, K, A, a_sm, a_sk, B, b_sn, b_sk, C, ldc,
+                                                                     alpha, beta);
+  } else {
+    dim3 grid((N + 31) / 32, (M + 31) / 32);
+    gemm_f32_strided_kernel<32><<<grid, 256, 0, as_stream(stream)>>>(M, N, K, A, a_sm, a_sk, B, b_sn, b_sk, C, ldc,
+                                                                     alpha, beta);
+  }
   PSRC_CHECK_LAUNCH();
   return PSRC_OK;
 }
