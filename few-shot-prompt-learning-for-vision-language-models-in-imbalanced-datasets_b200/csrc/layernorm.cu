@@ -9,6 +9,7 @@
 namespace psrc {
 
 constexpr int kLnWarps = 8;
+constexpr int kLnBwdWarps = 2;
 
 template <typename T>
 __device__ __forceinline__ void store4(T* p, float4 v);
@@ -102,14 +103,14 @@ ln_fwd_kernel(const float* __restrict__ x, const int32_t* __restrict__ idx, int 
 
 // dx_out[r] = (dx_in ? dx_in[r] : 0) + rstd * (g*dy - mean(g*dy) - xhat * mean(g*dy*xhat))
 // gathered form (L > 0): dy row s applies to x row s*L+idx[s]; every other row of dx_out is zeroed.
-template <typename T, typename TA, int NV>
-__global__ void __launch_bounds__(kLnWarps * 32)
+template <typename T, typename TA, int NV, int W>
+__global__ void __launch_bounds__(W * 32)
 ln_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x, const int32_t* __restrict__ idx, int L,
               const float* __restrict__ gamma, const float* __restrict__ mean_in,
               const float* __restrict__ rstd_in, const float* dx_in, float* dx_out, TA* __restrict__ dx_act,
               int rows, int D) {
   const int lane = threadIdx.x & 31;
-  const int r = blockIdx.x * kLnWarps + (threadIdx.x >> 5);  // row of x / dx
+  const int r = blockIdx.x * W + (threadIdx.x >> 5);  // row of x / dx
   if (r >= rows) return;
   int s = r;  // row of dy / mean / rstd
   if (L > 0) {
@@ -198,13 +199,14 @@ static int launch_bwd(const void* dy, const float* x, const int32_t* idx, int L,
                       const float* mean, const float* rstd, const float* dx_in, float* dx_out, void* dx_act,
                       int rows, int D, cudaStream_t s) {
   const int nv = (D + 127) / 128;
-  const int grid = (rows + kLnWarps - 1) / kLnWarps;
   const T* dyt = reinterpret_cast<const T*>(dy);
   TA* at = reinterpret_cast<TA*>(dx_act);
-#define LN_CASE(NV)                                                                                     \
-  case NV:                                                                                              \
-    ln_bwd_kernel<T, TA, NV><<<grid, kLnWarps * 32, 0, s>>>(dyt, x, idx, L, g, mean, rstd, dx_in, dx_out, \
-                                                            at, rows, D);                               \
+  // two rows per 64-thread block: at 92 registers per thread an 8-warp block leaves only 16 warps per SM and their
+  // load / reduce / store phases line up; small blocks measured 67.6 us vs 77.8 us (25 728 x 768, cold L2)
+#define LN_CASE(NV)                                                                                         \
+  case NV:                                                                                                  \
+    ln_bwd_kernel<T, TA, NV, kLnBwdWarps><<<(rows + kLnBwdWarps - 1) / kLnBwdWarps, kLnBwdWarps * 32, 0, s>>>( \
+        dyt, x, idx, L, g, mean, rstd, dx_in, dx_out, at, rows, D);                                         \
     break;
   switch (nv) {
     LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)

@@ -33,6 +33,31 @@ __global__ void im2col_kernel(const float* __restrict__ img, T* __restrict__ out
   }
 }
 
+// P % 8 == 0 (ViT-B/16, ViT-B/32), 16-bit output: eight elements per thread -- two 16-byte loads, one 16-byte store
+__global__ void im2col8_kernel(const float* __restrict__ img, __nv_bfloat16* __restrict__ out, int B, int R, int P,
+                               long long total8) {
+  const int G = R / P, PP = P * P, K = 3 * PP;
+  long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (; e < total8; e += stride) {
+    const long long el = e * 8;
+    const int col = (int)(el % K);
+    const long long row = el / K;
+    const int gx = (int)(row % G), gy = (int)((row / G) % G), b = (int)(row / ((long long)G * G));
+    const int c = col / PP, rem = col - c * PP, ky = rem / P, kx = rem - ky * P;
+    const float4* src = reinterpret_cast<const float4*>(
+        img + (((long long)(b * 3 + c) * R + gy * P + ky) * R + gx * P + kx));
+    const float4 v0 = __ldg(src), v1 = __ldg(src + 1);
+    uint4 u;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+    h[0] = __floats2bfloat162_rn(v0.x, v0.y);
+    h[1] = __floats2bfloat162_rn(v0.z, v0.w);
+    h[2] = __floats2bfloat162_rn(v1.x, v1.y);
+    h[3] = __floats2bfloat162_rn(v1.z, v1.w);
+    *reinterpret_cast<uint4*>(out + el) = u;
+  }
+}
+
 // One warp per token row: build the pre-LN row, LayerNorm it, write the fp32 residual stream.
 template <typename T, int NV>
 __global__ void __launch_bounds__(256)
@@ -241,7 +266,11 @@ extern "C" int psrc_im2col_patches(const float* image, void* patches, int out_dt
   if (B == 0) return PSRC_OK;
   const int G = R / P;
   const long long total2 = (long long)B * G * G * 3 * P * P / 2;
-  if (out_dtype == PSRC_BF16)
+  const bool al16 = ((reinterpret_cast<uintptr_t>(image) | reinterpret_cast<uintptr_t>(patches)) & 15) == 0;
+  if (out_dtype == PSRC_BF16 && P % 8 == 0 && R % 4 == 0 && al16)
+    im2col8_kernel<<<grid_for(total2 / 4, 256), 256, 0, as_stream(stream)>>>(
+        image, reinterpret_cast<__nv_bfloat16*>(patches), B, R, P, total2 / 4);
+  else if (out_dtype == PSRC_BF16)
     im2col_kernel<__nv_bfloat16><<<grid_for(total2, 256), 256, 0, as_stream(stream)>>>(
         image, reinterpret_cast<__nv_bfloat16*>(patches), B, R, P, total2);
   else
