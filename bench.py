@@ -327,7 +327,7 @@ def b200_arm(args):
             tot_f += f * cnt; tot_ms += t * cnt; n_launch += cnt
             del a, w, o
         ach = tot_f / (tot_ms * 1e-3) / 1e12
-        roof = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05.mma + TMA + TMEM)", "achieved": round(ach, 1),
+        roof = {"bound": "tensor", "kernel": "pair::gemm_pair_kernel (tcgen05.mma.cta_group::2 + TMA + TMEM)", "achieved": round(ach, 1),
                 "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": round(ach / peaks["tf_burst"], 4),
                 "peak_source": peaks["source"] + ", burst bf16 (kernel timed alone)", "traffic": gemm_traffic(),
                 "launches_per_step": n_launch, "avg_launch_us": round(tot_ms / n_launch * 1e3, 2),
