@@ -231,7 +231,9 @@ def check_attention(res: Results, backend_name: str):
                  (250, 11, 8, True), (2, 1, 2, True), (3, 16, 3, False), (5, 25, 1, True)]
     if backend_name == "tc":  # tcgen05 kernels: 32 < L <= 256
         cases = [(3, 201, 12, False), (5, 77, 8, True), (2, 197, 12, False), (2, 64, 2, False), (3, 128, 2, True),
-                 (2, 256, 2, False), (2, 129, 1, True), (37, 201, 12, False)]
+                 (2, 256, 2, False), (2, 129, 1, True), (37, 201, 12, False),
+                 # chunk geometries of the pipelined backward (L > 128): 10 / 11 / 15 / 9 column groups
+                 (2, 145, 2, False), (3, 176, 3, True), (2, 240, 1, False), (2, 130, 2, True)]
     for (n_seq, L, H, causal) in cases:
         D = H * 64
         for dtp in dts:
