@@ -16,6 +16,8 @@ from __future__ import annotations
 import math
 from dataclasses import dataclass, field
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -202,6 +204,8 @@ class PromptedClipStep:
             self.x0_end, self.dx0_end = e(self.Cl * self.Lt, self.Dt), e(self.Cl * self.Lt, self.Dt)
             self.zero_pos = torch.zeros_like(self.tpos)
         self.losses = e(4)
+        self.losses_host = torch.zeros(4, dtype=torch.float32).pin_memory() if dev.type == "cuda" else torch.zeros(4)
+        self._text_ahead = False     # True: the text-tower prefix of the NEXT step is already enqueued (graphs only)
         self.loss_scratch = e(4 * B + 2 * 296)
         self.labels = torch.zeros(B, device=dev, dtype=torch.int32)
         self.image = e(B, 3, a.image_resolution, a.image_resolution)
@@ -369,6 +373,7 @@ class PromptedClipStep:
         """The image-independent part of the forward: the text tower over this rank's class prompts (+ all-gather).
         Runs while the batch is still on its way to the device (`train_step_host`).  CoCoOp's text pass depends on
         the image features and therefore belongs to `forward_rest`."""
+        self._text_ahead = False     # an eager pass: whatever was enqueued ahead no longer counts
         if not self.per_image:
             self.text_features()
 
@@ -644,23 +649,94 @@ class PromptedClipStep:
         self.flat_param.copy_(keep[0])
         self.mom_buf.copy_(keep[1])
         self._graph = (g0, g1)
+        self._text_ahead = False
         return self._graph
+
+    # The text-tower prefix reads only the prompt parameters, so as soon as one step's SGD is enqueued the NEXT step's
+    # prefix can follow it on the stream: it then runs while the host is still waiting for this step's loss, logging
+    # and fetching the next batch (Dassl's loop calls `.item()` every iteration, promptsrc.py:330), instead of after.
+    # The loss terms are copied to pinned memory BEFORE that prefix is enqueued, so reading them does not wait for it.
+    text_ahead = os.environ.get("PSRC_TEXT_AHEAD", "1") != "0"
+
+    def invalidate_text(self):
+        """Call after changing prompt parameters from outside the step (load_state_dict, a foreign optimizer)."""
+        self._text_ahead = False
+
+    def _replay(self, wait_event=None):
+        g0, g1 = self._graph
+        main = torch.cuda.current_stream()
+        if g0 is not None and not self._text_ahead:
+            g0.replay()
+        if wait_event is not None:
+            main.wait_event(wait_event)
+        g1.replay()
+        self.losses_host.copy_(self.losses, non_blocking=True)
+        if getattr(self, "_loss_ready", None) is None:
+            self._loss_ready, self._step_done = torch.cuda.Event(), torch.cuda.Event()
+        self._loss_ready.record(main)
+        self._step_done.record(main)
+        self._text_ahead = False
+        if g0 is not None and self.text_ahead and self.cfg.world_size == 1:
+            g0.replay()
+            self._text_ahead = True
+
+    def loss_value(self) -> float:
+        """Sum of the step's loss terms on the host (the trainers' `loss.item()`), without waiting for work that was
+        enqueued after the step (the next step's text prefix)."""
+        if getattr(self, "_graph", None) is not None and getattr(self, "_loss_ready", None) is not None:
+            self._loss_ready.synchronize()
+            return float(self.losses_host.sum())
+        return float(self.losses.sum().item())
 
     def run(self):
         """One train step on the resident inputs: graph replay when captured, eager otherwise."""
         if getattr(self, "_graph", None) is not None:
-            if self._graph[0] is not None:
-                self._graph[0].replay()
-            self._graph[1].replay()
+            self._replay()
         else:
             self.train_step()
         return self.losses
 
-    def train_step_host(self, image_host: torch.Tensor, label_host: torch.Tensor) -> float:
+    def train_step_host(self, image_host: torch.Tensor, label_host: torch.Tensor, next_host=None) -> float:
         """The call the Dassl trainer makes per batch (PromptSRC.forward_backward, promptsrc.py:285-330):
-        host batch in (pinned fp32 [B,3,R,R], int64 [B]) -> H2D -> step -> SGD -> `loss.item()` (D2H sync)."""
-        self.run_host(image_host, label_host)
-        return float(self.losses.cpu().sum())                               # :330 (16-byte D2H)
+        host batch in (pinned fp32 [B,3,R,R], int64 [B]) -> H2D -> step -> SGD -> `loss.item()` (D2H sync).
+        `next_host = (image, label)` of the FOLLOWING batch, when the loader can look one batch ahead
+        (trainers.LookaheadLoader): its H2D copy is started behind this step's launch and runs under its compute."""
+        if getattr(self, "_staged_key", None) == id(image_host):
+            self.run_staged()
+        else:
+            self.run_host(image_host, label_host)
+        if next_host is not None:
+            self.stage_host(*next_host)
+        return self.loss_value()                                            # :330 (16-byte D2H)
+
+    def stage_host(self, image_host: torch.Tensor, label_host: torch.Tensor):
+        """Start the H2D copy of the NEXT batch into staging buffers on the copy stream and return at once."""
+        cs = getattr(self, "_copy_stream", None)
+        if cs is None:
+            cs = self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._copy_done = torch.cuda.Event()
+        if getattr(self, "image_next", None) is None:
+            self.image_next, self.labels_next = torch.empty_like(self.image), torch.empty_like(self.labels)
+            self._stage_done, self._stage_free = torch.cuda.Event(), None
+        if self._stage_free is not None:
+            cs.wait_event(self._stage_free)         # the previous batch has left the staging buffers
+        with torch.cuda.stream(cs):
+            self.image_next.copy_(image_host, non_blocking=True)
+            self.labels_next.copy_(label_host.to(torch.int32), non_blocking=True)
+            self._stage_done.record(cs)
+        self._staged_key = id(image_host)
+
+    def run_staged(self):
+        """One train step on the batch `stage_host` brought over: 77 MB device-to-device (24 us at cfg 3), then the step."""
+        main = torch.cuda.current_stream()
+        main.wait_event(self._stage_done)
+        self.image.copy_(self.image_next, non_blocking=True)
+        self.labels.copy_(self.labels_next, non_blocking=True)
+        if self._stage_free is None:
+            self._stage_free = torch.cuda.Event()
+        self._stage_free.record(main)
+        self._staged_key = None
+        return self.run()
 
     def run_host(self, image_host: torch.Tensor, label_host: torch.Tensor):
         """Batch in from the host (pinned: truly asynchronous) on a copy stream, overlapped with the image-independent
@@ -670,17 +746,16 @@ class PromptedClipStep:
         if cs is None:
             cs = self._copy_stream = torch.cuda.Stream(device=self.device)
             self._copy_done = torch.cuda.Event()
-        cs.wait_stream(main)                        # the previous step has finished reading self.image / self.labels
+        if self._text_ahead:
+            cs.wait_event(self._step_done)          # not the whole stream: the prefix enqueued ahead may still be running
+        else:
+            cs.wait_stream(main)                    # the previous step has finished reading self.image / self.labels
         with torch.cuda.stream(cs):
             self.image.copy_(image_host, non_blocking=True)                 # parse_batch_train :384-387
             self.labels.copy_(label_host.to(torch.int32), non_blocking=True)
             self._copy_done.record(cs)
-        graphs = getattr(self, "_graph", None)
-        if graphs is not None:
-            if graphs[0] is not None:
-                graphs[0].replay()
-            main.wait_event(self._copy_done)
-            graphs[1].replay()
+        if getattr(self, "_graph", None) is not None:
+            self._replay(wait_event=self._copy_done)
         else:
             self._step_part(0)
             main.wait_event(self._copy_done)

@@ -117,6 +117,37 @@ except Exception:  # noqa: BLE001 - any import problem means "no Dassl here"
                            osp.join(directory, n, model_name or f"model.pth.tar-{epoch + 1}"))
 
 
+class LookaheadLoader:
+    """Wraps Dassl's train loader (dassl/data/data_manager.py:13-52): yields every batch dict with the FOLLOWING batch
+    under "_next", so the trainer can start that batch's host-to-device copy behind the launch of the current step.
+    Batches, order and length are unchanged; the DataLoader's own workers already run ahead of the consumer."""
+
+    def __init__(self, loader):
+        self.loader = loader
+
+    def __len__(self):
+        return len(self.loader)
+
+    def __getattr__(self, name):
+        return getattr(self.loader, name)
+
+    def __iter__(self):
+        it = iter(self.loader)
+        cur = next(it, None)
+        while cur is not None:
+            nxt = next(it, None)
+            if isinstance(cur, dict):
+                cur = dict(cur)
+                cur["_next"] = nxt
+            yield cur
+            cur = nxt
+
+
+def _next_of(batch):
+    nxt = batch.get("_next") if isinstance(batch, dict) else None
+    return (nxt["img"], nxt["label"]) if isinstance(nxt, dict) else None
+
+
 def _get(node, path, default=None):
     """cfg.A.B.C with a default (the reference reads keys its own extend_cfg never defines)."""
     for k in path.split("."):
@@ -411,7 +442,7 @@ class _CustomCLIPBase(nn.Module):
                        dampening=float(_get(optim_cfg, "SGD_DAMPNING", 0.0)),
                        nesterov=bool(_get(optim_cfg, "SGD_NESTEROV", False)))
 
-    def train_step_fused(self, image, label, optim: FlatSGD):
+    def train_step_fused(self, image, label, optim: FlatSGD, next_batch=None):
         """The trainer's fast path: H2D of the batch, ONE CUDA-graph replay of forward + fused losses +
         prompt-only backward + SGD, and the loss terms left on the device (`.item()` is the caller's sync)."""
         st = self._step
@@ -422,15 +453,37 @@ class _CustomCLIPBase(nn.Module):
         if self._use_graph and getattr(st, "_graph", None) is None and self._eager_steps >= 1:
             st.capture(warmup=1)
         self._eager_steps += 1
+        # any torch-level in-place write to a trainable tensor (load_state_dict on a sub-module, a foreign optimizer,
+        # re-initialisation) bumps its version counter, the fused SGD kernel does not -- a text prefix enqueued
+        # ahead with the old values must then be recomputed
+        ver = sum(p._version for _, p in self._named_prompts)
+        if ver != getattr(self, "_param_version", None):
+            st.invalidate_text()
+            self._param_version = ver
         if image.is_cuda:
             st.image.copy_(image, non_blocking=True)
             st.labels.copy_(label.to(torch.int32), non_blocking=True)
             st.run()
+        elif getattr(st, "_staged_key", None) == id(image):
+            st.run_staged()                  # this batch was copied over while the previous step was running
         else:
             st.run_host(image, label)        # H2D on the copy stream, under the text-tower forward
+        if next_batch is not None and not next_batch[0].is_cuda and next_batch[0].shape[0] == st.cfg.batch:
+            st.stage_host(*next_batch)       # the following batch starts its H2D under this step's compute
         if self._infer is not None:
             self._infer.text_valid = False
         return st.losses
+
+    def step_loss(self, losses) -> float:
+        """`loss.item()` of the fused step (promptsrc.py:330): read from the pinned copy made right after the step, so the
+        host does not wait for the next step's text-tower prefix that is already enqueued behind it."""
+        return self._step.loss_value()
+
+    def load_state_dict(self, *args, **kwargs):
+        out = super().load_state_dict(*args, **kwargs)
+        if getattr(self, "_step", None) is not None:
+            self._step.invalidate_text()      # prompt parameters changed behind the step's back
+        return out
 
 
 def _focal_alpha_from_cfg(cfg, n_cls):
@@ -743,6 +796,9 @@ class _PromptTrainer(TrainerX):
         self.optim = self.model.make_optimizer(cfg.OPTIM)                    # SGD of optim/optimizer.py:105-113
         self.sched = build_scheduler(self.optim, cfg.OPTIM)
         self.register_model(self.MODEL_NAME, registered_module, self.optim, self.sched)
+        loader = getattr(self, "train_loader_x", None)                  # built before the model (trainer.py:325)
+        if loader is not None and not isinstance(loader, LookaheadLoader) and _get(cfg, "TRAINER.B200.LOOKAHEAD", True):
+            self.train_loader_x = LookaheadLoader(loader)
 
     def model_inference(self, input):
         return self.model(input)
@@ -796,8 +852,8 @@ class PromptSRC(_PromptTrainer):
 
     def forward_backward(self, batch):
         image, label = self.parse_batch_train(batch)
-        losses = self.model.train_step_fused(image, label, self.optim)
-        loss_summary = {"loss": float(losses.sum().item())}                  # promptsrc.py:330
+        losses = self.model.train_step_fused(image, label, self.optim, _next_of(batch))
+        loss_summary = {"loss": self.model.step_loss(losses)}                  # promptsrc.py:330
         last = (self.batch_idx + 1) == self.num_batches
         if _get(self.cfg, "TRAINER.PROMPTSRC.USE_GPA", False):               # promptsrc.py:335-360
             if last:
@@ -840,8 +896,8 @@ class CoOp(_PromptTrainer):
 
     def forward_backward(self, batch):
         image, label = self.parse_batch_train(batch)
-        losses = self.model.train_step_fused(image, label, self.optim)
-        loss_summary = {"loss": float(losses.sum().item())}
+        losses = self.model.train_step_fused(image, label, self.optim, _next_of(batch))
+        loss_summary = {"loss": self.model.step_loss(losses)}
         if self.model.loss_type == "ce":                                     # coop.py:461-469: accuracy of the UPDATED prompts
             st = self.model._step
             with torch.no_grad():
@@ -873,8 +929,8 @@ class MaPLe(_PromptTrainer):
 
     def forward_backward(self, batch):
         image, label = self.parse_batch_train(batch)
-        losses = self.model.train_step_fused(image, label, self.optim)
-        loss_summary = {"loss": float(losses.sum().item())}                  # maple.py:325
+        losses = self.model.train_step_fused(image, label, self.optim, _next_of(batch))
+        loss_summary = {"loss": self.model.step_loss(losses)}                  # maple.py:325
         if (self.batch_idx + 1) == self.num_batches:
             self.update_lr()
         return loss_summary
@@ -899,8 +955,8 @@ class CoCoOp(_PromptTrainer):
 
     def forward_backward(self, batch):
         image, label = self.parse_batch_train(batch)
-        losses = self.model.train_step_fused(image, label, self.optim)
-        loss_summary = {"loss": float(losses.sum().item())}                  # cocoop.py:328
+        losses = self.model.train_step_fused(image, label, self.optim, _next_of(batch))
+        loss_summary = {"loss": self.model.step_loss(losses)}                  # cocoop.py:328
         if (self.batch_idx + 1) == self.num_batches:
             self.update_lr()
         return loss_summary

@@ -85,3 +85,13 @@ def test_frozen_teacher_precompute_single_and_ensemble():
     _need_gpu()
     m = TC.check_teacher_ensemble()
     assert m["ensemble_rel"] < 2e-5 and m["single_rel"] < 2e-5, m
+
+
+def test_text_prefix_enqueued_ahead_is_exact_and_invalidated_by_outside_edits():
+    _need_gpu()
+    m = TC.check_text_ahead()
+    assert m["ahead_flag_True"] and not m["ahead_flag_False"], m
+    assert m["param_maxabs"] == 0.0 and m["loss_maxabs"] == 0.0, m
+    assert m["loss_jump_after_edit"] > 0.0, m
+    assert m["staged_steps_used"] and m["lookahead_losses_distinct"], m
+    assert m["lookahead_param_maxabs"] == 0.0 and m["lookahead_loss_maxabs"] == 0.0, m

@@ -308,6 +308,54 @@ def check_teacher_ensemble():
     return {"ensemble_rel": float((got - ref).norm() / ref.norm()), "single_rel": float((single - ref1).norm() / ref1.norm())}
 
 
+def check_text_ahead():
+    """The text-tower prefix enqueued ahead of the next step (step.PromptedClipStep._replay) must not change results:
+    a trainer with it and one without take the same steps, including across an in-place parameter edit made from
+    outside (what load_state_dict on a sub-module does), which has to invalidate the prefix computed ahead."""
+    from psrc_b200 import synthetic as S
+    out = {}
+    finals, losses = [], []
+    for ahead in (True, False):
+        tr, cfg, tokens = make_trainer("PromptSRC", "fp32")
+        tr.model._step.text_ahead = ahead
+        image, label = S.synthetic_batch(B, tokens.shape[0], 64, seed=1)
+        batch = {"img": image.pin_memory(), "label": label.pin_memory()}
+        ls = []
+        for s in range(6):
+            if s == 4:
+                with torch.no_grad():
+                    tr.model.prompt_learner.ctx.mul_(1.05)
+            tr.batch_idx = 0
+            ls.append(tr.forward_backward(batch)["loss"])
+        out[f"ahead_flag_{ahead}"] = bool(tr.model._step._text_ahead)
+        finals.append(torch.cat([p.detach().flatten().cpu() for _, p in sorted(tr.model.named_parameters()) if p.requires_grad]))
+        losses.append(ls)
+    out["param_maxabs"] = float((finals[0] - finals[1]).abs().max())
+    out["loss_maxabs"] = max(abs(a - b) for a, b in zip(*losses))
+    out["loss_jump_after_edit"] = abs(losses[0][4] - losses[0][3])
+    # the look-ahead loader (next batch copied over under the current step) against plain per-batch calls
+    from psrc_b200 import trainers as T
+    finals, losses = [], []
+    for look in (True, False):
+        tr, cfg, tokens = make_trainer("PromptSRC", "fp32")
+        batches = []
+        for i in range(5):
+            image, label = S.synthetic_batch(B, tokens.shape[0], 64, seed=10 + i)
+            batches.append({"img": image.pin_memory(), "label": label.pin_memory()})
+        ls = []
+        for b in (T.LookaheadLoader(batches) if look else batches):
+            tr.batch_idx = 0
+            ls.append(tr.forward_backward(b)["loss"])
+        finals.append(torch.cat([p.detach().flatten().cpu() for _, p in sorted(tr.model.named_parameters()) if p.requires_grad]))
+        losses.append(ls)
+        if look:
+            out["staged_steps_used"] = getattr(tr.model._step, "image_next", None) is not None
+    out["lookahead_param_maxabs"] = float((finals[0] - finals[1]).abs().max())
+    out["lookahead_loss_maxabs"] = max(abs(a - b) for a, b in zip(*losses))
+    out["lookahead_losses_distinct"] = len(set(round(x, 6) for x in losses[0])) > 1
+    return out
+
+
 def check_coop(prec="fp32", loss_type="ce"):
     import clip_oracle as O
     from psrc_b200 import synthetic as S
