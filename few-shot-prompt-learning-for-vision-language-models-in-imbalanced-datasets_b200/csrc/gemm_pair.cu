@@ -29,7 +29,6 @@ constexpr int kUmmaK = 16;
 constexpr int kEpiWarps = 8;    // two epilogue warps per TMEM lane quarter: even / odd 32-column chunks
 constexpr int kThreads = (4 + kEpiWarps) * 32;
 constexpr int kInSlots = 4;     // ring of prefetched residual / aux chunks (128 rows x 32 columns each)
-constexpr int kInSlotBytes = 128 * 128;   // fp32 chunk; a bf16 chunk uses the first half
 constexpr int kOutSlotBytes = 32 * 128;   // per epilogue warp: 32 rows x 32 fp32 (or bf16 out + bf16 out2)
 constexpr uint32_t kSpinLimit = 1u << 27;
 
@@ -51,16 +50,17 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
   return d;
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int IN_SLOTS, int IN_SLOT_BYTES>
 struct Smem {
   static constexpr int kABytes = kBMcta * kBK * 2;        // 16 KB
   static constexpr int kBBytes = (BN / 2) * kBK * 2;      // this CTA's half of the W tile
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kInOffset = STAGES * kStageBytes;
-  static constexpr int kOutOffset = kInOffset + kInSlots * kInSlotBytes;
+  static constexpr int kInSlotBytes = IN_SLOT_BYTES;
+  static constexpr int kOutOffset = kInOffset + IN_SLOTS * IN_SLOT_BYTES;
   static constexpr int kBarOffset = kOutOffset + kEpiWarps * kOutSlotBytes;   // one staging slot per epilogue warp
-  // full[STAGES] empty[STAGES] tmem_full[2] tmem_empty[2] in_full[kInSlots] in_empty[kInSlots] + tmem slot
-  static constexpr int kNumBars = 2 * STAGES + 4 + 2 * kInSlots;
+  // full[STAGES] empty[STAGES] tmem_full[2] tmem_empty[2] in_full[IN_SLOTS] in_empty[IN_SLOTS] + tmem slot
+  static constexpr int kNumBars = 2 * STAGES + 4 + 2 * IN_SLOTS;
   static constexpr int kTotal = kBarOffset + kNumBars * 8 + 16;
   static constexpr int kDyn = kTotal + 1024;               // slack for manual 1024 B alignment
 };
@@ -86,8 +86,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_out2,
                  const __grid_constant__ CUtensorMap tmap_in, Params p) {
-  using S = Smem<BN, STAGES>;
   constexpr bool kHasIn = (MODE == kGeluGrad || MODE == kResidual);
+  constexpr int kIn = kHasIn ? kInSlots : 0;   // epilogues without a second operand give the ring's 64 KB to the pipeline
+  using S = Smem<BN, STAGES, kIn, (MODE == kResidual) ? 128 * 128 : 128 * 64>;   // fp32 residual / bf16 aux chunk
   constexpr int kInRowBytes = (MODE == kResidual) ? 128 : 64;
   constexpr int kOutRowBytes = 32 * OUT_BYTES;
   constexpr int kChunks = BN / 32;
@@ -98,8 +99,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint64_t* tmem_full = empty_bar + STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
   uint64_t* in_full = tmem_empty + 2;
-  uint64_t* in_empty = in_full + kInSlots;
-  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(in_empty + kInSlots);
+  uint64_t* in_empty = in_full + kIn;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(in_empty + kIn);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -126,7 +127,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       mbar_init(&tmem_full[s], 1);   // multicast tcgen05.commit
       mbar_init(&tmem_empty[s], 2 * kEpiWarps);  // epilogue warps x 2 CTAs (leader's copy is the one used)
     }
-    for (int s = 0; s < kInSlots; ++s) {
+    for (int s = 0; s < kIn; ++s) {
       mbar_init(&in_full[s], 1);
       mbar_init(&in_empty[s], 4);
     }
@@ -208,8 +209,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if (col0 >= p.N) break;
           wait_bounded(&in_empty[slot], phase ^ 1);
           mbar_expect_tx(&in_full[slot], 128 * kInRowBytes);
-          tma_load_2d(&tmap_in, &in_full[slot], smem + S::kInOffset + slot * kInSlotBytes, col0, row0);
-          if (++slot == kInSlots) { slot = 0; phase ^= 1; }
+          tma_load_2d(&tmap_in, &in_full[slot], smem + S::kInOffset + slot * S::kInSlotBytes, col0, row0);
+          if (++slot == kIn) { slot = 0; phase ^= 1; }
         }
       }
     }
@@ -252,9 +253,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
         if (kHasIn) {
           const uint32_t g = gbase + (uint32_t)c;              // position of this chunk in the prefetch ring
-          const int islot = (int)(g % kInSlots);
-          wait_bounded(&in_full[islot], (g / kInSlots) & 1u);
-          const uint8_t* in = smem + S::kInOffset + islot * kInSlotBytes;
+          const int islot = (int)(g % (kIn > 0 ? kIn : 1));
+          wait_bounded(&in_full[islot], (g / (kIn > 0 ? kIn : 1)) & 1u);
+          const uint8_t* in = smem + S::kInOffset + islot * S::kInSlotBytes;
           if (MODE == kResidual) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -388,7 +389,7 @@ static int sm_count() {
 
 template <int BN, int STAGES, int MODE, int OUT_BYTES>
 static int launch(const psrc_gemm_args& a, cudaStream_t stream) {
-  using S = Smem<BN, STAGES>;
+  using S = Smem<BN, STAGES, (MODE == kGeluGrad || MODE == kResidual) ? kInSlots : 0, (MODE == kResidual) ? 128 * 128 : 128 * 64>;
   static_assert(S::kDyn <= 227 * 1024, "shared memory budget exceeded");
   auto kernel = gemm_pair_kernel<BN, STAGES, MODE, OUT_BYTES>;
   static bool attr_set = false;
@@ -438,6 +439,14 @@ static int launch_bn(const psrc_gemm_args& a, cudaStream_t stream) {
   if (force_bn == 128 || (force_bn == 0 && a.N <= 128)) return launch<128, 5, MODE, OUT_BYTES>(a, stream);
   // 256 x 192 tiles were measured for the N = 768 shapes (303 tiles = 4.09 -> 5 rounds on 74 pairs): 105 vs 98 us at
   // K = 3072 -- the narrower tile costs 0.9 of the wide one, so the extra round is not recovered.
+  // epilogues without a residual / aux operand: the 64 KB of the prefetch ring become two more pipeline stages
+  static const int deep = getenv("PSRC_PAIR_DEEP") ? atoi(getenv("PSRC_PAIR_DEEP")) : 1;
+  if constexpr (MODE == kNone || MODE == kGelu) {
+    if (deep) return launch<256, 6, MODE, OUT_BYTES>(a, stream);
+  }
+  if constexpr (MODE == kGeluGrad) {   // bf16 aux chunks are half the size of fp32 residual chunks: one more stage
+    if (deep) return launch<256, 5, MODE, OUT_BYTES>(a, stream);
+  }
   return launch<256, 4, MODE, OUT_BYTES>(a, stream);
 }
 
