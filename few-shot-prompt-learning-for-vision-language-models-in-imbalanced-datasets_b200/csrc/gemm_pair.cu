@@ -71,7 +71,6 @@ struct Params {
   const float* bias;
   float alpha;
   int has_out2;
-  int debug_skip;   // bandwidth experiment only (PSRC_PAIR_DEBUG_SKIP): 1 = no W loads, 2 = no A loads (wrong results)
 };
 
 // 16-byte chunk j of row r inside a staging box whose rows are RB bytes (128 -> SWIZZLE_128B, 64 -> SWIZZLE_64B)
@@ -155,11 +154,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           wait_bounded(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * S::kStageBytes;
           uint8_t* sb = sa + S::kABytes;
-          if (rank == 0)
-            mbar_expect_tx(&full_bar[stage], p.debug_skip == 1 ? 2 * S::kABytes
-                                             : p.debug_skip == 2 ? 2 * S::kBBytes : 2 * S::kStageBytes);
-          if (p.debug_skip != 2) tma_load_2d_pair(&tmap_a, &full_bar[stage], sa, kb * kBK, row_a);
-          if (p.debug_skip != 1) tma_load_2d_pair(&tmap_w, &full_bar[stage], sb, kb * kBK, row_w);
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * S::kStageBytes);
+          tma_load_2d_pair(&tmap_a, &full_bar[stage], sa, kb * kBK, row_a);
+          tma_load_2d_pair(&tmap_w, &full_bar[stage], sb, kb * kBK, row_w);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -418,8 +415,6 @@ static int launch(const psrc_gemm_args& a, cudaStream_t stream) {
   p.bias = a.bias;
   p.alpha = a.alpha;
   p.has_out2 = (MODE == kGelu && a.out2) ? 1 : 0;
-  static const int dbg = getenv("PSRC_PAIR_DEBUG_SKIP") ? atoi(getenv("PSRC_PAIR_DEBUG_SKIP")) : 0;
-  p.debug_skip = dbg;
   const int pairs = std::min(p.tiles_m * p.tiles_n, sm_count() / 2);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * pairs);
