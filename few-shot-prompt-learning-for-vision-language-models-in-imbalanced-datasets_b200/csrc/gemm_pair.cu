@@ -32,7 +32,9 @@ constexpr int kInSlots = 4;     // ring of prefetched residual / aux chunks (128
 constexpr int kOutSlotBytes = 32 * 128;   // per epilogue warp: 32 rows x 32 fp32 (or bf16 out + bf16 out2)
 constexpr uint32_t kSpinLimit = 1u << 27;
 
-enum Mode { kNone = 0, kGelu = 1, kGeluGrad = 2, kResidual = 3 };
+// kResidualInPlace: out aliases the residual (forward-only towers update the residual stream in place): the epilogue
+// stages alpha*acc + bias like kNone and lets the TMA store ADD it to global memory -- no residual bytes cross the SM
+enum Mode { kNone = 0, kGelu = 1, kGeluGrad = 2, kResidual = 3, kResidualInPlace = 4 };
 
 __device__ __forceinline__ void wait_bounded(uint64_t* bar, uint32_t parity) {
   for (uint32_t i = 0; !mbar_try_wait(bar, parity); ++i) {
@@ -310,7 +312,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         fence_async_proxy();   // generic-proxy smem writes -> visible to the TMA (async proxy)
         __syncwarp();
         if (lane == 0) {
-          tma_store_2d(&tmap_out, oslot, col0, row0);
+          if (MODE == kResidualInPlace) tma_reduce_add_2d(&tmap_out, oslot, col0, row0);
+          else tma_store_2d(&tmap_out, oslot, col0, row0);
           if (MODE == kGelu && p.has_out2) tma_store_2d(&tmap_out2, oslot + 2048, col0, row0);
           bulk_commit();
         }
@@ -436,7 +439,7 @@ static int launch_bn(const psrc_gemm_args& a, cudaStream_t stream) {
   // K = 3072 -- the narrower tile costs 0.9 of the wide one, so the extra round is not recovered.
   // epilogues without a residual / aux operand: the 64 KB of the prefetch ring become two more pipeline stages
   static const int deep = getenv("PSRC_PAIR_DEEP") ? atoi(getenv("PSRC_PAIR_DEEP")) : 1;
-  if constexpr (MODE == kNone || MODE == kGelu) {
+  if constexpr (MODE == kNone || MODE == kGelu || MODE == kResidualInPlace) {
     if (deep) return launch<256, 6, MODE, OUT_BYTES>(a, stream);
   }
   if constexpr (MODE == kGeluGrad) {   // bf16 aux chunks are half the size of fp32 residual chunks: one more stage
@@ -458,7 +461,8 @@ static int pair_mode(const psrc_gemm_args& a) {
   if (a.act == PSRC_ACT_QUICKGELU_GRAD && !a.residual && !a.out2 && a.aux_dtype == PSRC_BF16 &&
       a.out_dtype == PSRC_BF16)
     return pair::kGeluGrad;
-  if (a.act == PSRC_ACT_NONE && a.residual && !a.out2 && a.out_dtype == PSRC_F32) return pair::kResidual;
+  if (a.act == PSRC_ACT_NONE && a.residual && !a.out2 && a.out_dtype == PSRC_F32)
+    return (a.residual == a.out && a.ldres == a.ldo) ? pair::kResidualInPlace : pair::kResidual;
   return -1;
 }
 
@@ -481,6 +485,7 @@ int gemm_pair(const psrc_gemm_args& a, cudaStream_t stream) {
     case pair::kGelu: return pair::launch_bn<pair::kGelu, 2>(a, stream);
     case pair::kGeluGrad: return pair::launch_bn<pair::kGeluGrad, 2>(a, stream);
     case pair::kResidual: return pair::launch_bn<pair::kResidual, 4>(a, stream);
+    case pair::kResidualInPlace: return pair::launch_bn<pair::kResidualInPlace, 4>(a, stream);
   }
   set_error("gemm_pair: unsupported epilogue combination");
   return PSRC_ERR_UNSUPPORTED;

@@ -64,8 +64,10 @@ class Tower:
         M = self.M = n_seq * L
         e = lambda *s, dt=torch.float32: torch.empty(*s, device=device, dtype=dt)  # noqa: E731
         n_saved = self.nl if save else 1
-        self.X = [e(M, D) for _ in range(self.nl + 1 if save else 2)]
-        self.X1 = [e(M, D) for _ in range(n_saved)]
+        # a forward-only tower updates ONE residual-stream buffer in place (psrc_gemm then adds through the TMA store and
+        # no residual byte crosses the SM); a tower that is differentiated keeps every layer's LayerNorm inputs
+        self.X = [e(M, D) for _ in range(self.nl + 1 if save else 1)]
+        self.X1 = [e(M, D) for _ in range(n_saved)] if save else [self.X[0]]
         self.qkv = [e(M, 3 * D, dt=act) for _ in range(n_saved)]
         self.O = [e(M, D, dt=act) for _ in range(n_saved)]
         self.lse = [e(n_seq, H, L) for _ in range(n_saved)]
@@ -83,10 +85,10 @@ class Tower:
 
     # -- buffers of layer i
     def _xin(self, i):
-        return self.X[i] if self.save else self.X[i % 2]
+        return self.X[i] if self.save else self.X[0]
 
     def _xout(self, i):
-        return self.X[i + 1] if self.save else self.X[(i + 1) % 2]
+        return self.X[i + 1] if self.save else self.X[0]
 
     @property
     def x0(self):
@@ -94,7 +96,7 @@ class Tower:
 
     @property
     def x_final(self):
-        return self.X[self.nl] if self.save else self.X[self.nl % 2]
+        return self.X[self.nl] if self.save else self.X[0]
 
     def forward(self, prompts=None):
         """prompts: {layer i: fp32 [n_ctx, D] tensor}.  Input must already be in ``self.x0``."""

@@ -86,6 +86,10 @@ def check_gemm(res: Results, backend_name: str):
             rs = resid.clone()
             ops.gemm(a, w, rs, bias=bias, residual=rs, alpha=0.5, backend=backend)
             res.add(tag + " bias+res inplace", rel_err(rs, 0.5 * ref0 + bias + resid), 2e-3)
+            # the same, out of place (the differentiated towers keep every layer's residual stream)
+            ro = torch.full((M, N), float("nan"), device=dev)
+            ops.gemm(a, w, ro, bias=bias, residual=resid, alpha=0.5, backend=backend)
+            res.add(tag + " bias+res", rel_err(ro, 0.5 * ref0 + bias + resid), 2e-3)
             # quickgelu with pre-activation copy
             og = torch.empty(M, N, device=dev, dtype=dtp)
             pre = torch.empty(M, N, device=dev, dtype=dtp)
