@@ -69,7 +69,9 @@ typedef struct {
   int32_t act;
   int32_t aux_dtype;
   const void* aux; int64_t ldaux;
-  const float* residual; int64_t ldres; /* fp32 [M,N] or NULL; may alias out     */
+  const float* residual; int64_t ldres; /* fp32 [M,N] or NULL; may alias out: with   */
+                                        /* residual == out the sum is formed by the  */
+                                        /* TMA store (add at the L2), in place       */
   void* out; int64_t ldo; int32_t out_dtype;
   int32_t out2_dtype;
   void* out2; int64_t ldo2;    /* NULL or pre-activation (QUICKGELU only)        */
