@@ -304,31 +304,46 @@ def b200_arm(args):
     #      events on the launching stream; operands sized like the step's (A + out >> L2 for the big shapes)
     roof = None
     if not args.no_kernel_roofline and args.prec == "bf16":
-        shapes = flops.gemm_shapes(arch, B, step.Cl, step.Lt, 4, True, True)
+        shapes = flops.gemm_launches(arch, B, step.Cl, step.Lt, 4, True, True)
         tot_f, tot_ms, n_launch, per_shape = 0.0, 0.0, 0, []
-        for (M, N, K, cnt) in shapes:
+        for (M, N, K, cnt, mode) in shapes:
             if K % 8:
                 continue
             a = torch.randn(M, K, device=dev).to(torch.bfloat16)
             w = torch.randn(N, K, device=dev).to(torch.bfloat16)
-            o = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
             bias = torch.zeros(N, device=dev)
+            kw = {}
+            if mode in ("res", "res_inplace"):        # fp32 residual stream in / out
+                o = torch.empty(M, N, device=dev)
+                kw["residual"] = o if mode == "res_inplace" else torch.randn(M, N, device=dev)
+                kw["alpha"] = 1e-3                    # (in place: keeps the repeated accumulation finite)
+            else:
+                o = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+                if mode in ("gelu", "gelu_save"):
+                    kw["act"] = ops.ACT_QUICKGELU
+                    if mode == "gelu_save":
+                        kw["out2"] = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+                elif mode == "gelugrad":
+                    kw["act"] = ops.ACT_QUICKGELU_GRAD
+                    kw["aux"] = torch.randn(M, N, device=dev).to(torch.bfloat16)
+            if mode != "gelugrad":
+                kw["bias"] = bias
             for _ in range(3):
-                ops.gemm(a, w, o, bias=bias)
+                ops.gemm(a, w, o, **kw)
             reps = 20
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda.synchronize()
             e0.record()
             for _ in range(reps):
-                ops.gemm(a, w, o, bias=bias)
+                ops.gemm(a, w, o, **kw)
             e1.record()
             torch.cuda.synchronize()
             t = e0.elapsed_time(e1) / reps
             f = 2.0 * M * N * K
-            per_shape.append({"M": M, "N": N, "K": K, "count": cnt, "us": round(t * 1e3, 2),
+            per_shape.append({"M": M, "N": N, "K": K, "count": cnt, "epilogue": mode, "us": round(t * 1e3, 2),
                               "tflops": round(f / (t * 1e-3) / 1e12, 1)})
             tot_f += f * cnt; tot_ms += t * cnt; n_launch += cnt
-            del a, w, o
+            del a, w, o, kw
         ach = tot_f / (tot_ms * 1e-3) / 1e12
         roof = {"bound": "tensor", "kernel": "pair::gemm_pair_kernel (tcgen05.mma.cta_group::2 + TMA + TMEM)", "achieved": round(ach, 1),
                 "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": round(ach / peaks["tf_burst"], 4),

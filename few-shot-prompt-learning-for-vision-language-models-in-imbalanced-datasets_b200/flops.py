@@ -49,3 +49,25 @@ def gemm_shapes(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward):
         tower(B * (1 + P), Dv, arch.vision_layers, False)
     tower(C * Lt, Dt, arch.transformer_layers, True)
     return shapes
+
+
+def gemm_launches(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward):
+    """(M, N, K, count, epilogue) of every tcgen05 GEMM launch in one step, with the fused epilogue each one runs:
+    "none" (bias, 16-bit out), "res" (fp32 residual in, fp32 out), "res_inplace" (forward-only towers: the TMA store
+    adds), "gelu" / "gelu_save" (QuickGELU, + saved pre-activation), "gelugrad" (QuickGELU' * aux)."""
+    Dv, Dt, P = arch.vision_width, arch.transformer_width, arch.n_patches
+    out = [(B * P, Dv, 3 * arch.vision_patch_size ** 2, 1, "none")]
+
+    def tower(M, D, layers, bwd):
+        res, gelu = ("res", "gelu_save") if bwd else ("res_inplace", "gelu")
+        out.extend([(M, 3 * D, D, layers, "none"), (M, D, D, layers, res), (M, 4 * D, D, layers, gelu),
+                    (M, D, 4 * D, layers, res)])
+        if bwd:
+            out.extend([(M, 4 * D, D, layers, "gelugrad"), (M, D, 4 * D, layers, "none"), (M, D, D, layers, "none"),
+                        (M, D, 3 * D, layers, "none")])
+
+    tower(B * (1 + P + n_ctx_vision), Dv, arch.vision_layers, vision_backward)
+    if zero_shot:
+        tower(B * (1 + P), Dv, arch.vision_layers, False)
+    tower(C * Lt, Dt, arch.transformer_layers, True)
+    return out
