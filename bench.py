@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--prec", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--e2e-breakdown", action="store_true", help="diagnostic timings of the host-facing path (stderr)")
     ap.add_argument("--overlap-zs", type=int, default=1,
                     help="bit 0: frozen tower forward on a second stream (default on); bit 1: text backward on a second stream")
     ap.add_argument("--graph-multi", action="store_true", help="multi-GPU: capture the step incl. NCCL (experimental)")
@@ -292,6 +293,19 @@ def b200_arm(args):
     for _ in range(2):
         step.train_step_host(image_host, label_host, next_host=nxt)
     ms_e2e = timed(lambda: step.train_step_host(image_host, label_host, next_host=nxt), args.steps)
+    if args.e2e_breakdown and rank == 0 and world == 1:    # diagnostic: where does e2e - value go on this box?
+        again = timed(step.run, args.steps)
+        step.stage_host(*nxt)
+        nosync = timed(lambda: (step.run_staged(), step.stage_host(*nxt)), args.steps)
+        plain = timed(lambda: step.train_step_host(image_host, label_host), args.steps)
+        t0 = time.perf_counter()
+        for _ in range(20):
+            step.stage_host(*nxt)
+        torch.cuda.synchronize()
+        h2d = (time.perf_counter() - t0) / 20 * 1e3
+        print(f"[e2e breakdown] device-resident {ms_dev:.3f} ms, e2e {ms_e2e:.3f}, device-resident again {again:.3f}, "
+              f"staged without the per-step loss read {nosync:.3f}, no look-ahead {plain:.3f}, H2D alone {h2d:.3f} ms",
+              file=sys.stderr)
     clocks = sampler.stop() if rank == 0 else None
     loss_value = float(step.losses.sum())
 
