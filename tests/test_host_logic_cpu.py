@@ -136,3 +136,27 @@ def test_maple_cocoop_dropins_build_with_reference_names(monkeypatch):
     assert calls.count("attn_fwd") == 6 and calls.count("attn_bwd") == 3                   # vision fwd only, text fwd+bwd
     assert calls.count("prompt_grad") == TC.B and calls.count("ctx_bias_grad") == 1
     assert calls.count("group_logits_fwd") == 1 and calls.count("group_logits_bwd") == 1
+
+
+def test_lookahead_loader_yields_same_batches_with_the_following_one_attached():
+    """trainers.LookaheadLoader (drop-in around Dassl's train_loader_x): same batches, same order, same length, each with
+    the FOLLOWING batch under "_next" (None for the last), and attribute access falls through to the wrapped loader."""
+    from psrc_b200.trainers import LookaheadLoader, _next_of
+
+    class Loader(list):
+        dataset = "the-dataset"
+
+    batches = Loader({"img": torch.full((2, 3), float(i)), "label": torch.tensor([i, i])} for i in range(4))
+    la = LookaheadLoader(batches)
+    assert len(la) == 4 and la.dataset == "the-dataset"
+    for epoch in range(2):                      # re-iterable, like a DataLoader
+        seen = list(la)
+        assert [int(b["label"][0]) for b in seen] == [0, 1, 2, 3]
+        for i, b in enumerate(seen):
+            nxt = _next_of(b)
+            if i < 3:
+                assert nxt[0] is batches[i + 1]["img"] and nxt[1] is batches[i + 1]["label"]
+            else:
+                assert nxt is None
+    assert "_next" not in batches[0]            # the loader's own dicts are not modified
+    assert _next_of({"img": 1, "label": 2}) is None
