@@ -114,6 +114,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
       mbar_init(bar_o, 1);
       mbar_init(bar_e, 4);
       fence_mbar_init();
+      mbar_expect_tx(bar_load, 3 * n_mt * kTile);   // the loads do not depend on the TMEM allocation
+      for (int t = 0; t < n_mt; ++t) {
+        tma_load_3d(&tmap_qkv, bar_load, Qs + t * kTile, h * 64, t * 128, seq);
+        tma_load_3d(&tmap_qkv, bar_load, Ks + t * kTile, D + h * 64, t * 128, seq);
+        tma_load_3d(&tmap_qkv, bar_load, Vs + t * kTile, 2 * D + h * 64, t * 128, seq);
+      }
     }
     __syncwarp();
     tmem_alloc(tslot, 256);
@@ -126,12 +132,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
 
   if (warp == 4) {
     if (lane == 0) {
-      mbar_expect_tx(bar_load, 3 * n_mt * kTile);
-      for (int t = 0; t < n_mt; ++t) {
-        tma_load_3d(&tmap_qkv, bar_load, Qs + t * kTile, h * 64, t * 128, seq);
-        tma_load_3d(&tmap_qkv, bar_load, Ks + t * kTile, D + h * 64, t * 128, seq);
-        tma_load_3d(&tmap_qkv, bar_load, Vs + t * kTile, 2 * D + h * 64, t * 128, seq);
-      }
       wait_bounded(bar_load, 0);
       const uint32_t idesc_s = idesc_kk(Lp);
       const uint32_t ks = smem_u32(Ks), vs = smem_u32(Vs);
