@@ -863,6 +863,7 @@ class PromptSRC(_PromptTrainer):
             if self.step_counter == self.model.total_epochs + 1:
                 print("Using GPA model for final inference...")
                 self.model._step.flat_param.copy_(self.previous_model_gpa)
+                self.model._step.invalidate_text()       # a text prefix enqueued ahead used the pre-GPA prompts
         elif last:
             self.update_lr()
         return loss_summary
