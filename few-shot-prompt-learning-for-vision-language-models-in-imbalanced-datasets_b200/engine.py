@@ -60,6 +60,9 @@ class Tower:
         self.w, self.n_seq, self.L, self.D, self.H, self.causal = weights, n_seq, L, D, H, causal
         self.act, self.save, self.device = act, save, device
         self.prompt_layers = dict(prompt_layers or {})
+        # forward-only towers whose consumer reads only row 0 of every sequence (ln_post on the class token,
+        # model.py:426): the last block's MLP then runs on n_seq rows instead of n_seq * L (set by the owner)
+        self.cls_only_last_mlp = False
         self.nl = len(weights.blocks)
         M = self.M = n_seq * L
         e = lambda *s, dt=torch.float32: torch.empty(*s, device=device, dtype=dt)  # noqa: E731
@@ -75,6 +78,7 @@ class Tower:
         self.stats = [[e(M) for _ in range(4)] for _ in range(n_saved)]  # mean1, rstd1, mean2, rstd2
         self.h = e(M, D, dt=act)
         self.g = e(M, 4 * D, dt=act)
+        self.hc = e(n_seq, D, dt=act)            # class-token rows of the last block (cls_only_last_mlp)
         if save:
             assert weights.need_backward
             self.du = e(M, 4 * D, dt=act)
@@ -112,6 +116,14 @@ class Tower:
             ops.gemm(self.h, b.wqkv, self.qkv[s], bias=b.bqkv)
             ops.attn_fwd(self.qkv[s], self.O[s], self.lse[s], n_seq, L, H, self.causal)
             ops.gemm(self.O[s], b.wo, x1, bias=b.bo, residual=x0)
+            if self.cls_only_last_mlp and not self.save and i == self.nl - 1:
+                # x1 is x2 here (in place); only the class-token rows go through LN2 and the MLP, as a strided view
+                xc = x1.view(n_seq, L, D)[:, 0]
+                gc = self.g[:n_seq]
+                ops.gather_ln_fwd(x1, None, b.ln2_g, b.ln2_b, self.hc, None, None, n_seq, L, D)
+                ops.gemm(self.hc, b.w1, gc, bias=b.b1, act=ACT_QUICKGELU)
+                ops.gemm(gc, b.w2, xc, bias=b.b2, residual=xc)
+                continue
             ops.layernorm_fwd(x1, b.ln2_g, b.ln2_b, self.h, mean2, rstd2)
             ops.gemm(self.h, b.w1, self.g, bias=b.b1, act=ACT_QUICKGELU, out2=self.u[s] if self.save else None)
             ops.gemm(self.g, b.w2, x2, bias=b.b2, residual=x1)

@@ -23,7 +23,8 @@ def step_flops(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward, text_ba
     out["patch_embed"] = 2 * B * P * (3 * arch.vision_patch_size ** 2) * Dv
     out["vision_fwd"] = arch.vision_layers * block_fwd(B, Lv, Dv)
     out["vision_bwd"] = arch.vision_layers * block_bwd(B, Lv, Dv) if vision_backward else 0
-    out["frozen_vision_fwd"] = arch.vision_layers * block_fwd(B, 1 + P, Dv) if zero_shot else 0
+    # (the frozen tower's last block runs its MLP on the class-token rows only: 16 D^2 per skipped row)
+    out["frozen_vision_fwd"] = (arch.vision_layers * block_fwd(B, 1 + P, Dv) - B * P * 16 * Dv * Dv) if zero_shot else 0
     out["text_fwd"] = arch.transformer_layers * block_fwd(C, Lt, Dt)
     out["text_bwd"] = arch.transformer_layers * block_bwd(C, Lt, Dt) if text_backward else 0
     heads = 2 * B * Dv * E * (2 if zero_shot else 1) + 2 * C * Dt * E
@@ -58,16 +59,19 @@ def gemm_launches(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward):
     Dv, Dt, P = arch.vision_width, arch.transformer_width, arch.n_patches
     out = [(B * P, Dv, 3 * arch.vision_patch_size ** 2, 1, "none")]
 
-    def tower(M, D, layers, bwd):
+    def tower(M, D, layers, bwd, cls_rows=0):
         res, gelu = ("res", "gelu_save") if bwd else ("res_inplace", "gelu")
-        out.extend([(M, 3 * D, D, layers, "none"), (M, D, D, layers, res), (M, 4 * D, D, layers, gelu),
-                    (M, D, 4 * D, layers, res)])
+        mlp_layers = layers - 1 if cls_rows else layers        # forward-only vision tower: last MLP on class-token rows
+        out.extend([(M, 3 * D, D, layers, "none"), (M, D, D, layers, res), (M, 4 * D, D, mlp_layers, gelu),
+                    (M, D, 4 * D, mlp_layers, res)])
+        if cls_rows:
+            out.extend([(cls_rows, 4 * D, D, 1, gelu), (cls_rows, D, 4 * D, 1, res)])
         if bwd:
             out.extend([(M, 4 * D, D, layers, "gelugrad"), (M, D, 4 * D, layers, "none"), (M, D, D, layers, "none"),
                         (M, D, 3 * D, layers, "none")])
 
     tower(B * (1 + P + n_ctx_vision), Dv, arch.vision_layers, vision_backward)
     if zero_shot:
-        tower(B * (1 + P), Dv, arch.vision_layers, False)
+        tower(B * (1 + P), Dv, arch.vision_layers, False, cls_rows=B)
     tower(C * Lt, Dt, arch.transformer_layers, True)
     return out

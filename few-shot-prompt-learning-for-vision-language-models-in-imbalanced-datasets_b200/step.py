@@ -181,6 +181,8 @@ class PromptedClipStep:
                         t_prompts)
         self.zt = Tower(self.vw, B, 1 + P, self.Dv, a.vision_heads, False, self.act, False, dev) \
             if cfg.zero_shot_branch else None
+        if self.zt is not None:
+            self.zt.cls_only_last_mlp = True    # only ln_post(x[:, 0]) of the frozen tower is ever read (:301)
 
         e = lambda *s, dt=torch.float32: torch.empty(*s, device=dev, dtype=dt)  # noqa: E731
         self.patches = e(B * P, 3 * a.vision_patch_size ** 2, dt=self.act)
@@ -777,6 +779,7 @@ class VisionInference:
         P = a.n_patches
         v_prompts = {i: (1 + P, cfg.n_ctx_vision) for i in range(1, cfg.depth_vision)} if cfg.n_ctx_vision > 0 else {}
         self.vt = Tower(step.vw, batch, step.Lv, step.Dv, a.vision_heads, False, act, False, dev, v_prompts)
+        self.vt.cls_only_last_mlp = True        # evaluation reads ln_post(x[:, 0]) only
         e = lambda *s, dt=torch.float32: torch.empty(*s, device=dev, dtype=dt)  # noqa: E731
         self.image = e(batch, 3, a.image_resolution, a.image_resolution)
         self.patches = e(batch * P, 3 * a.vision_patch_size ** 2, dt=act)
