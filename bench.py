@@ -3,6 +3,8 @@
 
   python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun)
   python bench.py --impl reference ...                      CPU arm: the oracle port on host cores
+  python bench.py --config coop_c100_b32 | cocoop_c365_b8 | maple_l14_c1000 | infer512_maple_l14 | infer512_promptsrc
+                                                            the other BASELINE.json configs (default: promptsrc_c1000)
 
 A "step" = one PromptSRC train step over one synthetic batch: prompted ViT-B/16 (4 deep visual prompts,
 depth 9) over B images, text transformer over the rank's class shard of C = 1000 prompts, cosine logits,
@@ -28,6 +30,28 @@ for _p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
 METRIC = "train_images_per_sec"
 UNIT = "img/s"
 
+# BASELINE.json configs; the driver's N = 1 line is the default (configs[2], the one `metric` is quoted on)
+CONFIGS = {
+    "promptsrc_c1000": dict(trainer="PromptSRC", arch="ViT-B/16", batch=128, classes=1000, baseline="configs[2]",
+                            workload="PromptSRC ViT-B/16 train step, ImageNet-LT-shaped 1000 classes, 4+4 deep V/L "
+                                     "prompts depth 9 (BASELINE.json configs[2])"),
+    "coop_c100_b32": dict(trainer="CoOp", arch="ViT-B/16", batch=32, classes=100, baseline="configs[1]",
+                          workload="CoOp ViT-B/16 train step, 16 learnable context tokens, CIFAR-100-LT-shaped 100 "
+                                   "classes (imbalance 100), focal CE (BASELINE.json configs[1])"),
+    "cocoop_c365_b8": dict(trainer="CoCoOp", arch="ViT-B/16", batch=8, classes=365, baseline="configs[3]",
+                           workload="CoCoOp ViT-B/16 train step, meta-net conditioned context, one text pass per "
+                                    "image, Places-LT-shaped 365 classes, focal CE (BASELINE.json configs[3])"),
+    "maple_l14_c1000": dict(trainer="MaPLe", arch="ViT-L/14", batch=128, classes=1000, baseline="configs[4]",
+                            workload="MaPLe ViT-L/14 train step, coupled prompts (2 tokens, depth 9), "
+                                     "ImageNet-LT-shaped 1000 classes, focal CE (BASELINE.json configs[4])"),
+    "infer512_maple_l14": dict(trainer="MaPLe", arch="ViT-L/14", batch=512, classes=1000, baseline="configs[4]",
+                               infer=True, workload="MaPLe ViT-L/14 inference sweep, batch 512, cached text features "
+                                                    "(BASELINE.json configs[4])"),
+    "infer512_promptsrc": dict(trainer="PromptSRC", arch="ViT-B/16", batch=512, classes=1000, baseline="configs[2]",
+                               infer=True, workload="PromptSRC ViT-B/16 inference sweep, batch 512, cached text "
+                                                    "features (SURVEY 8f-1)"),
+}
+
 
 def parse_args():
     ap = argparse.ArgumentParser()
@@ -35,8 +59,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=128, help="images per GPU (weak) / global (strong)")
-    ap.add_argument("--classes", type=int, default=1000)
+    ap.add_argument("--config", default="promptsrc_c1000", choices=list(CONFIGS))
+    ap.add_argument("--batch", type=int, default=None, help="images per GPU (weak) / global (strong); default per config")
+    ap.add_argument("--classes", type=int, default=None)
     ap.add_argument("--prec", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-graph", action="store_true")
@@ -46,10 +71,17 @@ def parse_args():
     ap.add_argument("--graph-multi", action="store_true", help="multi-GPU: capture the step incl. NCCL (experimental)")
     ap.add_argument("--no-truncate", action="store_true", help="run all 77 text positions (dense-equivalent)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-torch-gpu-baseline", action="store_true",
+                    help="skip the torch-on-B200 bar (the oracle modules on cuda: fp32 / bf16 autocast / truncated / SDPA)")
+    ap.add_argument("--no-strong-record", action="store_true", help="N > 1: skip the strong-scaling sub-record")
     ap.add_argument("--no-kernel-roofline", action="store_true")
     ap.add_argument("--cpu-sample-batch", type=int, default=8)
     ap.add_argument("--cpu-sample-classes", type=int, default=64)
-    return ap.parse_args()
+    args = ap.parse_args()
+    c = CONFIGS[args.config]
+    args.batch = args.batch or c["batch"]
+    args.classes = args.classes or c["classes"]
+    return args
 
 
 def load_peaks():
@@ -125,84 +157,277 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------ CPU arm (oracle port on host cores)
-def cpu_oracle_leg(args, steps, warmup):
-    """The oracle restatement of the reference PromptSRC step (oracle/clip_oracle.py: fp32 PyTorch + autograd,
-    dense 77 text positions exactly like the reference) timed on the host cores on a bounded, proportional
-    sample of cfg #3: `cpu_sample_batch` images with `cpu_sample_classes` classes (same classes-per-image
-    ratio as 128 : 1000), forward + backward + SGD."""
-    import torch
-    import clip_oracle as O
-    import psrc_b200  # noqa: F401
-    from psrc_b200 import synthetic as S
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
+def _oracle_promptsrc_closure(torch, O, S, B, C, device="cpu", truncate=False, dtype=None):
+    """One reference-equivalent PromptSRC train step (forward + backward + SGD) through the oracle restatement
+    (oracle/clip_oracle.py, pinned on the unmodified reference by oracle/make_golden*.py) as a closure."""
     arch = S.ARCHS["ViT-B/16"]
-    B, C, depth, n_ctx = args.cpu_sample_batch, args.cpu_sample_classes, 9, 4
-    sd = S.make_clip_state_dict(arch, seed=0)
-    tokens = torch.as_tensor(S.load_token_fixture()[:C])
+    depth, n_ctx = 9, 4
+    sd = {k: v.to(device) for k, v in S.make_clip_state_dict(arch, seed=0).items()}
+    tokens = torch.as_tensor(S.load_token_fixture()[:C]).to(device)
     image, label = S.synthetic_batch(B, C, arch.image_resolution, seed=1)
-    fixed = O.teacher_text_features(sd, tokens, arch.transformer_heads, truncate=int(tokens.argmax(-1).max()) + 1)
+    image, label = image.to(device), label.to(device)
+    trunc = int(tokens.argmax(-1).max()) + 1
+    fixed = O.teacher_text_features(sd, tokens, arch.transformer_heads, truncate=trunc)
     deep = S.make_deep_prompts(arch, n_ctx, n_ctx, depth, depth, seed=100)
     params = [sd["token_embedding.weight"][tokens[0, 1:1 + n_ctx]].clone(), deep["visual.VPT"].clone()]
     params += [deep[f"visual.transformer.resblocks.{i}.VPT_shallow"].clone() for i in range(1, depth)]
     params += [deep[f"transformer.resblocks.{i}.VPT_shallow"].clone() for i in range(1, depth)]
-    params = [p.requires_grad_(True) for p in params]
+    params = [p.to(device).requires_grad_(True) for p in params]
     opt = torch.optim.SGD(params, lr=0.0025, momentum=0.9, weight_decay=5e-4)
 
     def one():
         ctx, vpt = params[0], params[1]
         dv = {i: params[1 + i] for i in range(1, depth)}
         dtx = {i: params[depth + i] for i in range(1, depth)}
-        o = O.promptsrc_step(sd, tokens, image, label, ctx, vpt, dv, dtx, fixed, n_ctx, arch.vision_heads,
-                             arch.transformer_heads)
+        with torch.autocast(device_type=str(device).split(":")[0], dtype=dtype, enabled=dtype is not None):
+            o = O.promptsrc_step(sd, tokens, image, label, ctx, vpt, dv, dtx, fixed, n_ctx, arch.vision_heads,
+                                 arch.transformer_heads, truncate=trunc if truncate else None)
         opt.zero_grad()
         o["loss"].backward()
         opt.step()
-        return float(o["loss"].detach())
+        return o["loss"].detach()
+    return one
 
+
+def cpu_oracle_leg(args, steps, warmup, threads=None):
+    """The oracle restatement of the reference PromptSRC step (fp32 PyTorch + autograd, dense 77 text positions exactly
+    like the reference) timed on the host cores on a bounded, proportional sample of cfg #3: `cpu_sample_batch` images
+    with `cpu_sample_classes` classes (same classes-per-image ratio as 128 : 1000), forward + backward + SGD."""
+    import torch
+    import clip_oracle as O
+    import psrc_b200  # noqa: F401
+    from psrc_b200 import synthetic as S
+    cores = threads or (os.cpu_count() or 1)
+    torch.set_num_threads(cores)
+    B, C = args.cpu_sample_batch, args.cpu_sample_classes
+    one = _oracle_promptsrc_closure(torch, O, S, B, C)
     for _ in range(warmup):
         one()
     t0 = time.perf_counter()
     for _ in range(steps):
-        one()
+        float(one())
     dt = (time.perf_counter() - t0) / steps
+    torch.set_num_threads(os.cpu_count() or 1)
     return {"value": B / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "pinned_by": "oracle/make_golden.py + make_golden_full.py assert this port against the unmodified reference "
+                         "modules (tests/golden/*.npz; /root/reference is absent on the GPU box)",
             "sample": f"PromptSRC ViT-B/16 fp32 step (fwd+bwd+SGD), {B} images x {C} classes, 77 text positions, "
                       f"{steps} timed steps after {warmup} warm-up, {dt:.2f} s/step, torch CPU {cores} threads"}, dt
 
 
 def reference_arm(args):
+    """`--impl reference`: the reference's CPU implementation of the path (the pinned port) on the host cores.  The
+    `config` block states what RAN: a bounded sample (8 images x 64 classes by default), not the B200 arm's batch."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     steps, warmup = max(1, min(args.steps, 3)), max(1, min(args.warmup, 1))
     cb, dt = cpu_oracle_leg(args, steps, warmup)
+    one_thread, dt1 = cpu_oracle_leg(args, 1, 0, threads=1)
+    cb["one_thread"] = {"value": one_thread["value"], "unit": UNIT, "ms_per_step": dt1 * 1e3}
+    B, C = args.cpu_sample_batch, args.cpu_sample_classes
+    cfgd = {"workload": CONFIGS["promptsrc_c1000"]["workload"] + " -- BOUNDED CPU SAMPLE",
+            "global_batch": B, "per_gpu_batch": None, "classes": C, "text_positions": 77,
+            "sample_of": {"config": "BASELINE.json configs[2]", "global_batch": 128, "classes": 1000},
+            "same_config_as_b200_arm": False, "parallelism": f"torch CPU, {cb['cores']} threads"}
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": steps, "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": args.scaling,
-            "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": workload_config(args, args.gpus, None, cpu=True),
-            "cpu_baseline": cb,
+            "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "config": cfgd, "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, world, Lt, cpu=False):
-    gb = args.batch * world if args.scaling == "weak" else args.batch
-    return {"workload": "PromptSRC ViT-B/16 train step, ImageNet-LT-shaped 1000 classes, 4+4 deep V/L prompts depth 9 "
-                        "(BASELINE.json configs[2])",
-            "global_batch": gb, "per_gpu_batch": gb // world, "classes": args.classes,
-            "parallelism": f"dp{world} images x class-sharded text tower (all-gather t_hat / reduce-scatter dt_hat)",
-            "text_positions": (77 if cpu else Lt),
+def torch_gpu_leg(args, dev, B, C):
+    """SURVEY 2.2 / 8(d) "the bar to beat": the same modules (the pinned restatement of the reference's PyTorch code) on
+    the B200 under torch's own kernels (cuBLAS(Lt), ATen / SDPA), full cfg #3 (C = 1000, B = 128), forward + backward +
+    SGD, CUDA events.  Variants: fp32 (TF32 off) dense 77 positions = the reference as shipped; bf16 autocast; bf16 +
+    text truncated to max(EOT)+1 (the same exact shortcut the B200 arm uses); bf16 + truncation + fused SDPA attention."""
+    import torch
+    import clip_oracle as O
+    from psrc_b200 import synthetic as S
+    out = {}
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    variants = [("fp32_dense77", None, False, False), ("bf16_autocast_dense77", torch.bfloat16, False, False),
+                ("bf16_autocast_truncated", torch.bfloat16, True, False),
+                ("bf16_autocast_truncated_sdpa", torch.bfloat16, True, True)]
+    for name, dtype, trunc, sdpa in variants:
+        try:
+            O.USE_SDPA = sdpa
+            one = _oracle_promptsrc_closure(torch, O, S, B, C, device=dev, truncate=trunc, dtype=dtype)
+            one(); one()
+            torch.cuda.synchronize()
+            n = 2 if dtype is None else 5
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                one()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / n
+            out[name] = {"ms_per_step": round(ms, 2), "img_per_s": round(B / (ms * 1e-3), 1)}
+        except Exception as ex:  # noqa: BLE001  (an OOM of the torch baseline must not take the bench line down)
+            out[name] = {"error": f"{type(ex).__name__}: {str(ex)[:120]}"}
+        finally:
+            O.USE_SDPA = False
+            one = None
+            torch.cuda.empty_cache()
+    return out
+
+
+def workload_config(args, world, Lt, B):
+    c = CONFIGS[args.config]
+    gb = B * world
+    return {"workload": c["workload"], "config": args.config, "global_batch": gb, "per_gpu_batch": B,
+            "classes": args.classes,
+            "parallelism": (f"dp{world} images, every rank runs all classes (CoCoOp: per-image text passes)"
+                            if c["trainer"] == "CoCoOp" else
+                            f"dp{world} images x class-sharded text tower (all-gather t_hat / reduce-scatter dt_hat)"),
+            "text_positions": Lt,
             "l2": "per-step working set (saved activations, several GB) exceeds the 126 MB L2; no explicit flush"}
 
 
 # ------------------------------------------------------------------ B200 arm
+def build_step(args, B, world, rank, pg, dev):
+    """PromptedClipStep of `args.config` on seeded synthetic weights / tokens (no network: random-init CLIP)."""
+    import torch
+    from psrc_b200 import synthetic as S
+    from psrc_b200.step import PromptedClipStep, StepConfig, encode_text_frozen
+    c = CONFIGS[args.config]
+    arch = S.ARCHS[c["arch"]]
+    C = args.classes
+    sd = S.make_clip_state_dict(arch, seed=0)
+    tr = c["trainer"]
+    common = dict(arch=arch, n_cls=C, batch=B, prec=args.prec, world_size=world, rank=rank, process_group=pg,
+                  truncate_text=not args.no_truncate)
+    fixed = None
+    if tr == "PromptSRC":
+        tokens = torch.as_tensor(S.load_token_fixture()[:C])
+        cfg = StepConfig(n_ctx_text=4, n_ctx_vision=4, depth_text=9, depth_vision=9, zero_shot_branch=True, **common)
+        fixed = encode_text_frozen(sd, tokens, dev, prec="fp32")               # frozen teacher, init-time
+    elif tr == "CoOp":
+        tokens = torch.as_tensor(S.load_token_fixture("tokens_x16_object1000")[:C])
+        alpha = S.focal_alpha(S.lt_counts_cifar100(C, 500, 0.01), C)
+        cfg = StepConfig(n_ctx_text=16, n_ctx_vision=0, depth_text=1, depth_vision=0, focal_alpha=alpha, **common)
+    elif tr == "CoCoOp":
+        tokens = torch.as_tensor(S.load_token_fixture()[:C])
+        alpha = S.focal_alpha(S.lt_counts_pareto(C, seed=5), C)
+        cfg = StepConfig(n_ctx_text=4, n_ctx_vision=0, depth_text=1, depth_vision=0, per_image_text=True,
+                         meta_hidden=arch.embed_dim // 16, focal_alpha=alpha, **common)
+    else:  # MaPLe
+        tokens = torch.as_tensor(S.load_token_fixture()[:C])
+        alpha = S.focal_alpha(S.lt_counts_pareto(C), C)
+        cfg = StepConfig(n_ctx_text=2, n_ctx_vision=2, depth_text=9, depth_vision=9, coupling=True, focal_alpha=alpha,
+                         **common)
+    step = PromptedClipStep(cfg, sd, tokens, dev, fixed_embeddings=fixed)
+    n_ctx = cfg.n_ctx_text
+    with torch.no_grad():
+        if tr == "CoOp":
+            step.params["ctx"].copy_(torch.randn(16, arch.transformer_width,
+                                                 generator=torch.Generator().manual_seed(11)) * 0.02)
+        else:
+            step.params["ctx"].copy_(sd["token_embedding.weight"][tokens[0, 1:1 + n_ctx]])
+        if tr == "PromptSRC":
+            deep = S.make_deep_prompts(arch, 4, 4, 9, 9, seed=100)
+            step.params["vpt"].copy_(deep["visual.VPT"])
+            for i in range(1, 9):
+                step.params[f"vision.{i}"].copy_(deep[f"visual.transformer.resblocks.{i}.VPT_shallow"])
+                step.params[f"text.{i}"].copy_(deep[f"transformer.resblocks.{i}.VPT_shallow"])
+        elif tr == "MaPLe":
+            mp_ = S.make_maple_params(arch, 2, 9, seed=200)
+            for k in step.params:
+                if k == "ctx":
+                    continue
+                parts = k.split(".")
+                if parts[0] == "text":
+                    src = f"compound_prompts_text.{int(parts[1]) - 1}"
+                else:
+                    kind, i = ("weight" if parts[1] == "w" else "bias"), int(parts[2])
+                    src = f"proj.{kind}" if i == 0 else f"compound_prompt_projections.{i - 1}.{kind}"
+                step.params[k].copy_(mp_[src])
+        elif tr == "CoCoOp":
+            mp_ = S.make_cocoop_params(arch, seed=300)
+            names = {"meta.w1": "meta_net.linear1.weight", "meta.b1": "meta_net.linear1.bias",
+                     "meta.w2": "meta_net.linear2.weight", "meta.b2": "meta_net.linear2.bias"}
+            for k, src in names.items():
+                step.params[k].copy_(mp_[src])
+    lr = {"PromptSRC": 0.0025, "MaPLe": 0.0035}.get(tr, 0.002)
+    step.init_optimizer(lr=lr, momentum=0.9, weight_decay=5e-4)
+    step.overlap_zero_shot = bool(args.overlap_zs & 1)
+    step.overlap_backward = bool(args.overlap_zs & 2)
+    return step, arch
+
+
+def flop_model(args, arch, step, B, Lt):
+    """(executed, dense-equivalent) step FLOPs of this rank and the GEMM launch list, per config."""
+    from psrc_b200 import flops
+    tr = CONFIGS[args.config]["trainer"]
+    n_text = step.n_text_seq
+    ncv = step.cfg.n_ctx_vision
+    zs, vb = step.cfg.zero_shot_branch, ncv > 0
+    fl = flops.step_flops(arch, B, n_text, Lt, ncv, zs, vb)
+    dense = flops.step_flops(arch, B, n_text, 77, ncv, zs, vb)
+    shapes = flops.gemm_launches(arch, B, n_text, Lt, ncv, zs, vb, vision_cls_rows=(B if not vb else 0))
+    _ = tr
+    return fl, dense, shapes
+
+
+def gemm_roofline(torch, ops, dev, shapes, peaks, ms_dev):
+    """Every GEMM launch of the step timed alone with CUDA events on the launching stream, operands sized like the
+    step's, with the fused epilogue it runs in the step; launch-weighted TFLOP/s against the measured burst peak."""
+    tot_f, tot_ms, n_launch, per_shape = 0.0, 0.0, 0, []
+    for (M, N, K, cnt, mode) in shapes:
+        if K % 8 or cnt == 0:
+            continue
+        a = torch.randn(M, K, device=dev).to(torch.bfloat16)
+        w = torch.randn(N, K, device=dev).to(torch.bfloat16)
+        bias = torch.zeros(N, device=dev)
+        kw = {}
+        if mode in ("res", "res_inplace"):        # fp32 residual stream in / out
+            o = torch.empty(M, N, device=dev)
+            kw["residual"] = o if mode == "res_inplace" else torch.randn(M, N, device=dev)
+            kw["alpha"] = 1e-3                    # (in place: keeps the repeated accumulation finite)
+        else:
+            o = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+            if mode in ("gelu", "gelu_save"):
+                kw["act"] = ops.ACT_QUICKGELU
+                if mode == "gelu_save":
+                    kw["out2"] = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+            elif mode == "gelugrad":
+                kw["act"] = ops.ACT_QUICKGELU_GRAD
+                kw["aux"] = torch.randn(M, N, device=dev).to(torch.bfloat16)
+        if mode != "gelugrad":
+            kw["bias"] = bias
+        for _ in range(3):
+            ops.gemm(a, w, o, **kw)
+        reps = 20
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            ops.gemm(a, w, o, **kw)
+        e1.record()
+        torch.cuda.synchronize()
+        t = e0.elapsed_time(e1) / reps
+        f = 2.0 * M * N * K
+        per_shape.append({"M": M, "N": N, "K": K, "count": cnt, "epilogue": mode, "us": round(t * 1e3, 2),
+                          "tflops": round(f / (t * 1e-3) / 1e12, 1)})
+        tot_f += f * cnt; tot_ms += t * cnt; n_launch += cnt     # noqa: E702
+        del a, w, o, kw
+    ach = tot_f / (tot_ms * 1e-3) / 1e12
+    return {"bound": "tensor", "kernel": "pair::gemm_pair_kernel (tcgen05.mma.cta_group::2 + TMA + TMEM)",
+            "achieved": round(ach, 1), "peak": peaks["tf_burst"], "unit": "TFLOP/s",
+            "frac": round(ach / peaks["tf_burst"], 4),
+            "peak_source": peaks["source"] + ", burst bf16 (kernel timed alone)", "traffic": gemm_traffic(),
+            "launches_per_step": n_launch, "avg_launch_us": round(tot_ms / n_launch * 1e3, 2),
+            "gemm_share_of_step": round(tot_ms / ms_dev, 3), "per_shape": per_shape}
+
+
 def b200_arm(args):
     import torch
     import torch.distributed as dist
     import psrc_b200  # noqa: F401
-    from psrc_b200 import cabi, flops, ops, synthetic as S
-    from psrc_b200.step import PromptedClipStep, StepConfig, encode_text_frozen
+    from psrc_b200 import cabi, ops
 
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py --impl b200 needs a CUDA device: there is no CPU fallback")
@@ -220,46 +445,7 @@ def b200_arm(args):
         pg = dist.group.WORLD
     cabi.load()
     peaks = load_peaks()
-
-    arch = S.ARCHS["ViT-B/16"]
-    C = args.classes
-    B = args.batch if args.scaling == "weak" else args.batch // world
-    tokens = torch.as_tensor(S.load_token_fixture()[:C])
-    sd = S.make_clip_state_dict(arch, seed=0)
-    shots = S.lt_counts_pareto(C)
-    cfg = StepConfig(arch=arch, n_cls=C, batch=B, prec=args.prec, n_ctx_text=4, n_ctx_vision=4, depth_text=9,
-                     depth_vision=9, zero_shot_branch=True, world_size=world, rank=rank, process_group=pg,
-                     truncate_text=not args.no_truncate)
-    fixed = encode_text_frozen(sd, tokens, dev, prec="fp32")               # frozen teacher, init-time
-    step = PromptedClipStep(cfg, sd, tokens, dev, fixed_embeddings=fixed)
-    deep = S.make_deep_prompts(arch, 4, 4, 9, 9, seed=100)
-    with torch.no_grad():
-        step.params["ctx"].copy_(sd["token_embedding.weight"][tokens[0, 1:5]])
-        step.params["vpt"].copy_(deep["visual.VPT"])
-        for i in range(1, 9):
-            step.params[f"vision.{i}"].copy_(deep[f"visual.transformer.resblocks.{i}.VPT_shallow"])
-            step.params[f"text.{i}"].copy_(deep[f"transformer.resblocks.{i}.VPT_shallow"])
-    step.init_optimizer(lr=0.0025, momentum=0.9, weight_decay=5e-4)
-    step.overlap_zero_shot = bool(args.overlap_zs & 1)
-    step.overlap_backward = bool(args.overlap_zs & 2)
-    del sd
-    g = torch.Generator().manual_seed(1 + rank)
-    image_host = torch.randn(B, 3, arch.image_resolution, arch.image_resolution, generator=g).pin_memory()
-    label_host = torch.randint(0, C, (B,), generator=g).pin_memory()       # int64, as Dassl hands it over
-    step.image.copy_(image_host)
-    step.labels.copy_(label_host.to(torch.int32))
-    torch.cuda.synchronize()
-
-    # launches per step (eager pass, counted by the library)
-    n0 = cabi.launch_count()
-    step.train_step()
-    torch.cuda.synchronize()
-    launches = cabi.launch_count() - n0
-    # multi-GPU: eager by default -- capturing the NCCL collectives was measured at N=2 (24.47 vs 24.57 ms/step: the
-    # step is not launch-bound) and the captured communicator did not shut down cleanly, so it stays opt-in
-    use_graph = not args.no_graph and (world == 1 or args.graph_multi)
-    if use_graph:
-        step.capture(warmup=1)
+    conf = CONFIGS[args.config]
 
     def barrier():
         if world > 1:
@@ -279,6 +465,30 @@ def b200_arm(args):
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms) / steps
+
+    if conf.get("infer"):
+        return infer_arm(args, world, rank, local, pg, dev, peaks, timed)
+
+    C = args.classes
+    B = args.batch if args.scaling == "weak" else args.batch // world
+    step, arch = build_step(args, B, world, rank, pg, dev)
+    g = torch.Generator().manual_seed(1 + rank)
+    image_host = torch.randn(B, 3, arch.image_resolution, arch.image_resolution, generator=g).pin_memory()
+    label_host = torch.randint(0, C, (B,), generator=g).pin_memory()       # int64, as Dassl hands it over
+    step.image.copy_(image_host)
+    step.labels.copy_(label_host.to(torch.int32))
+    torch.cuda.synchronize()
+
+    # launches per step (eager pass, counted by the library)
+    n0 = cabi.launch_count()
+    step.train_step()
+    torch.cuda.synchronize()
+    launches = cabi.launch_count() - n0
+    # multi-GPU: eager by default -- capturing the NCCL collectives was measured at N=2 (24.47 vs 24.57 ms/step: the
+    # step is not launch-bound) and the captured communicator did not shut down cleanly, so it stays opt-in
+    use_graph = not args.no_graph and (world == 1 or args.graph_multi)
+    if use_graph:
+        step.capture(warmup=1)
 
     sampler = ClockSampler(local)
     for _ in range(max(3, args.warmup)):
@@ -310,70 +520,78 @@ def b200_arm(args):
     loss_value = float(step.losses.sum())
 
     gb = B * world
-    fl = flops.step_flops(arch, B, step.Cl, step.Lt, 4, True, True)
-    dense = flops.step_flops(arch, B, step.Cl, 77, 4, True, True)
+    fl, dense, shapes = flop_model(args, arch, step, B, step.Lt)
     tf_step = fl["total"] / (ms_dev * 1e-3) / 1e12                          # per rank
+    Lt = step.Lt
 
-    # ---- roofline of the dominant kernel (tcgen05 GEMM): every GEMM shape of the step timed alone with CUDA
-    #      events on the launching stream; operands sized like the step's (A + out >> L2 for the big shapes)
     roof = None
     if not args.no_kernel_roofline and args.prec == "bf16":
-        shapes = flops.gemm_launches(arch, B, step.Cl, step.Lt, 4, True, True)
-        tot_f, tot_ms, n_launch, per_shape = 0.0, 0.0, 0, []
-        for (M, N, K, cnt, mode) in shapes:
-            if K % 8:
-                continue
-            a = torch.randn(M, K, device=dev).to(torch.bfloat16)
-            w = torch.randn(N, K, device=dev).to(torch.bfloat16)
-            bias = torch.zeros(N, device=dev)
-            kw = {}
-            if mode in ("res", "res_inplace"):        # fp32 residual stream in / out
-                o = torch.empty(M, N, device=dev)
-                kw["residual"] = o if mode == "res_inplace" else torch.randn(M, N, device=dev)
-                kw["alpha"] = 1e-3                    # (in place: keeps the repeated accumulation finite)
-            else:
-                o = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
-                if mode in ("gelu", "gelu_save"):
-                    kw["act"] = ops.ACT_QUICKGELU
-                    if mode == "gelu_save":
-                        kw["out2"] = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
-                elif mode == "gelugrad":
-                    kw["act"] = ops.ACT_QUICKGELU_GRAD
-                    kw["aux"] = torch.randn(M, N, device=dev).to(torch.bfloat16)
-            if mode != "gelugrad":
-                kw["bias"] = bias
-            for _ in range(3):
-                ops.gemm(a, w, o, **kw)
-            reps = 20
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            torch.cuda.synchronize()
-            e0.record()
-            for _ in range(reps):
-                ops.gemm(a, w, o, **kw)
-            e1.record()
-            torch.cuda.synchronize()
-            t = e0.elapsed_time(e1) / reps
-            f = 2.0 * M * N * K
-            per_shape.append({"M": M, "N": N, "K": K, "count": cnt, "epilogue": mode, "us": round(t * 1e3, 2),
-                              "tflops": round(f / (t * 1e-3) / 1e12, 1)})
-            tot_f += f * cnt; tot_ms += t * cnt; n_launch += cnt
-            del a, w, o, kw
-        ach = tot_f / (tot_ms * 1e-3) / 1e12
-        roof = {"bound": "tensor", "kernel": "pair::gemm_pair_kernel (tcgen05.mma.cta_group::2 + TMA + TMEM)", "achieved": round(ach, 1),
-                "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": round(ach / peaks["tf_burst"], 4),
-                "peak_source": peaks["source"] + ", burst bf16 (kernel timed alone)", "traffic": gemm_traffic(),
-                "launches_per_step": n_launch, "avg_launch_us": round(tot_ms / n_launch * 1e3, 2),
-                "gemm_share_of_step": round(tot_ms / ms_dev, 3), "per_shape": per_shape}
+        roof = gemm_roofline(torch, ops, dev, shapes, peaks, ms_dev)
 
-    cpu_b = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu_b, _ = cpu_oracle_leg(args, steps=2, warmup=1)
+    # ---- N > 1: what the same per-rank work costs on ONE GPU without any collective (captured graphs) = `ideal_ms`,
+    #      and the strong-scaling record at the contract's global batch (global B = 128, B / N per rank)
+    scaling_records = None
+    if world > 1:
+        scaling_records = {}
+        a1 = argparse.Namespace(**vars(args))
+        a1.classes = step.Cl
+        local_step, _ = build_step(a1, B, 1, 0, None, dev)
+        local_step.image.copy_(image_host)
+        local_step.labels.copy_(label_host.to(torch.int32) % step.Cl)
+        local_step.train_step()
+        local_step.capture(warmup=1)
+        for _ in range(3):
+            local_step.run()
+        ideal = timed(local_step.run, args.steps)
+        scaling_records["weak"] = {"global_batch": gb, "per_gpu_batch": B, "classes_per_rank": step.Cl,
+                                   "ms_per_step": ms_dev, "value": gb / (ms_dev * 1e-3),
+                                   "ideal_ms": ideal, "ms_over_ideal": round(ms_dev / ideal, 4),
+                                   "ideal_is": "the same per-rank shapes (B images, C/N classes) as a single-GPU "
+                                               "graph-captured step with no collective, timed on this box"}
+        del local_step
+        if not args.no_strong_record and args.scaling == "weak" and args.batch % world == 0:
+            Bs = args.batch // world
+            del step
+            torch.cuda.empty_cache()
+            sstep, _ = build_step(args, Bs, world, rank, pg, dev)
+            sstep.image.copy_(image_host[:Bs])
+            sstep.labels.copy_(label_host[:Bs].to(torch.int32))
+            for _ in range(3):
+                sstep.run()
+            ms_s = timed(sstep.run, args.steps)
+            a1.classes = sstep.Cl
+            ls, _ = build_step(a1, Bs, 1, 0, None, dev)
+            ls.image.copy_(image_host[:Bs])
+            ls.labels.copy_(label_host[:Bs].to(torch.int32) % sstep.Cl)
+            ls.train_step()
+            ls.capture(warmup=1)
+            for _ in range(3):
+                ls.run()
+            ideal_s = timed(ls.run, args.steps)
+            scaling_records["strong"] = {"global_batch": args.batch, "per_gpu_batch": Bs, "classes_per_rank": sstep.Cl,
+                                         "ms_per_step": ms_s, "value": args.batch / (ms_s * 1e-3),
+                                         "ideal_ms": ideal_s, "ms_over_ideal": round(ms_s / ideal_s, 4)}
+            del sstep, ls
+
+    cpu_b, torch_gpu = None, None
+    if rank == 0 and world == 1 and args.config == "promptsrc_c1000":
+        if not args.no_torch_gpu_baseline:
+            step = None
+            torch.cuda.empty_cache()
+            torch_gpu = torch_gpu_leg(args, dev, B, C)
+            for v in torch_gpu.values():
+                if "ms_per_step" in v:
+                    v["b200_arm_speedup"] = round(v["ms_per_step"] / ms_dev, 2)
+        if not args.no_cpu_baseline:
+            cpu_b, _ = cpu_oracle_leg(args, steps=2, warmup=1)
+            one_thread, dt1 = cpu_oracle_leg(args, 1, 0, threads=1)
+            cpu_b["one_thread"] = {"value": one_thread["value"], "unit": UNIT, "ms_per_step": dt1 * 1e3}
 
     if rank == 0:
         line = {"metric": METRIC, "value": gb / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(3, args.warmup), "ms_per_step": ms_dev, "higher_is_better": True,
                 "scaling": args.scaling, "vs_baseline": None, "dtype": args.prec, "data": "synthetic",
-                "config": workload_config(args, world, step.Lt),
+                "config": workload_config(args, world, Lt, B),
                 "e2e": {"value": gb / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                         "h2d_bytes_per_step": image_host.numel() * 4 + label_host.numel() * 8,
                         "d2h_bytes_per_step": 16, "api": "PromptedClipStep.train_step_host (pinned host batch; the following batch's H2D is issued under the step)"},
@@ -384,7 +602,73 @@ def b200_arm(args):
                 "step_mfu_vs_nominal_2250": round(tf_step / 2250.0, 4),
                 "executed_tflop_per_step_per_gpu": round(fl["total"] / 1e12, 3),
                 "dense_equiv_tflop_per_step_per_gpu": round(dense["total"] / 1e12, 3),
-                "roofline": roof, "cpu_baseline": cpu_b}
+                "roofline": roof, "cpu_baseline": cpu_b, "torch_gpu_reference": torch_gpu,
+                "scaling_records": scaling_records}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def infer_arm(args, world, rank, local, pg, dev, peaks, timed):
+    """Evaluation sweep with cached text features (Dassl `SimpleTrainer.test`, engine/trainer.py:445-486):
+    text features once (class-sharded + all-gather), then per batch of 512 images: vision forward + cosine logits +
+    argmax.  `value` = images/s with the batch resident; `e2e` = pinned host batch -> H2D -> logits -> predictions D2H."""
+    import torch
+    import torch.distributed as dist
+    from psrc_b200 import cabi, flops
+    from psrc_b200.step import VisionInference
+    Bi = args.batch
+    a_train = argparse.Namespace(**vars(args))
+    step, arch = build_step(a_train, 8, world, rank, pg, dev)       # the train-step buffers are not used: tiny batch
+    inf = VisionInference(step, Bi)
+    g = torch.Generator().manual_seed(1 + rank)
+    image_host = torch.randn(Bi, 3, arch.image_resolution, arch.image_resolution, generator=g).pin_memory()
+    image = image_host.to(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    inf.refresh_text()
+    torch.cuda.synchronize()
+    e0.record()
+    inf.refresh_text()
+    e1.record()
+    torch.cuda.synchronize()
+    text_once_ms = e0.elapsed_time(e1)
+    n0 = cabi.launch_count()
+    inf.logits_for(image)
+    torch.cuda.synchronize()
+    launches = cabi.launch_count() - n0
+    sampler = ClockSampler(local)
+    for _ in range(max(3, args.warmup)):
+        inf.logits_for(image)
+    if rank == 0:
+        sampler.start()
+    ms_dev = timed(lambda: inf.logits_for(image), args.steps)
+    pred_host = torch.empty(Bi, dtype=torch.int64).pin_memory()
+
+    def e2e_once():
+        img = image_host.to(dev, non_blocking=True)
+        pred_host.copy_(inf.logits_for(img).argmax(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    for _ in range(2):
+        e2e_once()
+    ms_e2e = timed(e2e_once, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    Dv, P = arch.vision_width, arch.n_patches
+    Lv = inf.vt.L
+    f_img = arch.vision_layers * flops.block_fwd(1, Lv, Dv) - (Lv - 1) * 16 * Dv * Dv + 2 * P * 3 * arch.vision_patch_size ** 2 * Dv
+    tf = f_img * Bi / (ms_dev * 1e-3) / 1e12
+    if rank == 0:
+        gb = Bi * world
+        line = {"metric": "inference_images_per_sec", "value": gb / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world,
+                "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_dev, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": args.prec, "data": "synthetic",
+                "config": workload_config(args, world, step.Lt, Bi),
+                "e2e": {"value": gb / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                        "h2d_bytes_per_step": image_host.numel() * 4, "d2h_bytes_per_step": Bi * 8,
+                        "api": "VisionInference.logits_for(host batch -> device) + argmax -> pinned host"},
+                "text_features_once_ms": round(text_once_ms, 3), "gpu_launches": launches * args.steps,
+                "gpu_launches_per_step": launches, "clocks": clocks,
+                "step_tflops_per_gpu": round(tf, 1), "step_mfu_vs_sustained": round(tf / peaks["tf_sustained"], 4),
+                "executed_tflop_per_step_per_gpu": round(f_img * Bi / 1e12, 3)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

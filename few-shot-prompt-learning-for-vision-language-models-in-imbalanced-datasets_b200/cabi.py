@@ -78,6 +78,8 @@ SIGNATURES = {
     "psrc_group_logits_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     "psrc_ctx_bias_grad": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "psrc_permute_rows": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "psrc_crop_resize_normalize": (_i, [_vp, _i64, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i,
+                                        C.POINTER(_f), C.POINTER(_f), _vp]),
 }
 
 _lib = None

@@ -22,6 +22,8 @@ def step_flops(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward, text_ba
     out = {}
     out["patch_embed"] = 2 * B * P * (3 * arch.vision_patch_size ** 2) * Dv
     out["vision_fwd"] = arch.vision_layers * block_fwd(B, Lv, Dv)
+    if not vision_backward:   # forward-only prompted tower (CoOp / CoCoOp): last MLP on the class-token rows only
+        out["vision_fwd"] -= B * (Lv - 1) * 16 * Dv * Dv
     out["vision_bwd"] = arch.vision_layers * block_bwd(B, Lv, Dv) if vision_backward else 0
     # (the frozen tower's last block runs its MLP on the class-token rows only: 16 D^2 per skipped row)
     out["frozen_vision_fwd"] = (arch.vision_layers * block_fwd(B, 1 + P, Dv) - B * P * 16 * Dv * Dv) if zero_shot else 0
@@ -52,7 +54,7 @@ def gemm_shapes(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward):
     return shapes
 
 
-def gemm_launches(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward):
+def gemm_launches(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward, vision_cls_rows=0):
     """(M, N, K, count, epilogue) of every tcgen05 GEMM launch in one step, with the fused epilogue each one runs:
     "none" (bias, 16-bit out), "res" (fp32 residual in, fp32 out), "res_inplace" (forward-only towers: the TMA store
     adds), "gelu" / "gelu_save" (QuickGELU, + saved pre-activation), "gelugrad" (QuickGELU' * aux)."""
@@ -70,7 +72,8 @@ def gemm_launches(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward):
             out.extend([(M, 4 * D, D, layers, "gelugrad"), (M, D, 4 * D, layers, "none"), (M, D, D, layers, "none"),
                         (M, D, 3 * D, layers, "none")])
 
-    tower(B * (1 + P + n_ctx_vision), Dv, arch.vision_layers, vision_backward)
+    tower(B * (1 + P + n_ctx_vision), Dv, arch.vision_layers, vision_backward,
+          cls_rows=0 if vision_backward else vision_cls_rows)
     if zero_shot:
         tower(B * (1 + P), Dv, arch.vision_layers, False, cls_rows=B)
     tower(C * Lt, Dt, arch.transformer_layers, True)

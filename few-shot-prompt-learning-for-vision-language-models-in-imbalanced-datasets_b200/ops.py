@@ -252,3 +252,19 @@ def permute_rows(src, perm, dst, n_seq, L, D, add=None, inverse=False):
     cabi.check(cabi.load().psrc_permute_rows(ptr(src), ptr(perm), ptr(add), ptr(dst), n_seq, L, D, int(inverse),
                                              cabi.stream()), "psrc_permute_rows")
     return dst
+
+
+def crop_resize_normalize(src_u8, geom_f, geom_i, out, interpolation, quantize, max_taps, mean, std):
+    """uint8 [B, Hc, Wc, 3] canvases + per-image geometry -> normalised fp32 [B, 3, R, R] (psrc_crop_resize_normalize)."""
+    B, Hc, Wc, ch = src_u8.shape
+    R = out.shape[-1]
+    assert src_u8.dtype == torch.uint8 and ch == 3 and src_u8.is_contiguous()
+    assert out.shape == (B, 3, R, R) and out.dtype == torch.float32 and out.is_contiguous()
+    assert geom_f.shape == (B, 4) and geom_f.dtype == torch.float32 and geom_f.is_contiguous()
+    assert geom_i.shape == (B, 5) and geom_i.dtype == torch.int32 and geom_i.is_contiguous()
+    m3, s3 = (C.c_float * 3)(*mean), (C.c_float * 3)(*std)
+    cabi.check(cabi.load().psrc_crop_resize_normalize(ptr(src_u8), Hc * Wc * 3, Wc * 3, ptr(geom_f), ptr(geom_i),
+                                                      ptr(out), B, R, int(interpolation), int(quantize),
+                                                      int(max_taps), m3, s3, cabi.stream()),
+               "psrc_crop_resize_normalize")
+    return out

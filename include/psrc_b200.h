@@ -265,6 +265,26 @@ int psrc_axpy(float* y, const float* x, float a, int64_t n, psrc_stream_t stream
 int psrc_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n,
               psrc_stream_t stream);
 
+/* ---------------------------------------------------- input pipeline
+ * uint8 HWC images -> CLIP-normalised fp32 [B,3,R,R] in one launch.  Replaces the per-image PIL /
+ * torchvision chain Dassl composes (Dassl.pytorch/dassl/data/transforms/transforms.py:176-326 train:
+ * RandomResizedCrop -> RandomHorizontalFlip -> ToTensor -> Normalize; :329-357 test: Resize ->
+ * CenterCrop -> ToTensor -> Normalize); the random parameters are drawn on the host with the
+ * reference's own RNG calls (psrc_b200/input_pipeline.py) and arrive here as geometry:
+ *   src      uint8, image b at src + b*image_stride, pixel (y,x,c) at y*row_stride + 3*x + c
+ *   geom_f   [B,4] fp32  {sx, sy, ox, oy}: source centre of output pixel x = (x + ox + 0.5) * sx
+ *   geom_i   [B,5] int32 {left, top, w, h, flip}: the sampled window (coordinates are relative to
+ *            its origin and the filter taps are clamped to it), flip = mirror the output columns
+ *   interpolation 0 = bilinear, 1 = bicubic (a = -0.5), both antialiased like PIL (support scaled by
+ *            max(scale, 1)); quantize 0 = float, 1 = round the result to uint8 (the PIL image
+ *            handed to ToTensor), 2 = also round after the horizontal pass (PIL's two-pass resize)
+ *   max_taps >= the largest filter window of the batch (host-computed: 2*ceil(support)+2)
+ *   mean_host / std_host: 3 HOST floats (cfg.INPUT.PIXEL_MEAN / PIXEL_STD)                        */
+int psrc_crop_resize_normalize(const uint8_t* src, int64_t image_stride, int32_t row_stride,
+                               const float* geom_f, const int32_t* geom_i, float* out, int32_t B,
+                               int32_t R, int32_t interpolation, int32_t quantize, int32_t max_taps,
+                               const float* mean_host, const float* std_host, psrc_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -23,6 +23,9 @@ import torch
 import torch.nn.functional as F
 
 LN_EPS = 1e-5
+# bench.py's torch-on-B200 leg only: route the attention core through F.scaled_dot_product_attention (the fused kernel
+# nn.MultiheadAttention's fast path uses on torch 2.x); the default is the explicit softmax(QK^T)V restatement.
+USE_SDPA = False
 
 
 def fp16_rt(x: torch.Tensor) -> torch.Tensor:
@@ -54,9 +57,12 @@ def attention(x, sd, p, n_head, causal):
     q = q.view(N, L, n_head, hd).transpose(1, 2)
     k = k.view(N, L, n_head, hd).transpose(1, 2)
     v = v.view(N, L, n_head, hd).transpose(1, 2)
+    if USE_SDPA:
+        a = F.scaled_dot_product_attention(q, k, v, is_causal=causal).transpose(1, 2).reshape(N, L, D)
+        return a @ sd[p + "attn.out_proj.weight"].t() + sd[p + "attn.out_proj.bias"]
     s = (q @ k.transpose(-1, -2)) / math.sqrt(hd)
     if causal:
-        s = s + torch.full((L, L), float("-inf")).triu(1)
+        s = s + torch.full((L, L), float("-inf"), device=x.device).triu(1)
     a = (s.softmax(-1) @ v).transpose(1, 2).reshape(N, L, D)
     return a @ sd[p + "attn.out_proj.weight"].t() + sd[p + "attn.out_proj.bias"]
 
@@ -111,7 +117,7 @@ def text_tower(prompts, eot_idx, sd, n_head, deep=None, n_ctx=0, half_prompts=Tr
             x = torch.cat([x[:, :1], rt(deep[i].expand(C, -1, -1)), x[:, 1 + n_ctx:]], dim=1)  # :246-252
         x = block(x, sd, f"transformer.resblocks.{i}.", n_head, causal=True)
     x = layer_norm(x, sd["ln_final.weight"], sd["ln_final.bias"])  # :64
-    return x[torch.arange(C), eot_idx] @ sd["text_projection"]     # :68
+    return x[torch.arange(C, device=x.device), eot_idx] @ sd["text_projection"]     # :68
 
 
 def normalize(x):

@@ -92,7 +92,8 @@ def maple_setup(arch_name, depth, tokens, device, prec, batch, n_ctx=2, sd=None,
     return step, sd, mp_
 
 
-def coop_setup(arch_name, tokens, device, prec, batch, ctx0, n_ctx=16, sd=None, focal_alpha=None, position="end"):
+def coop_setup(arch_name, tokens, device, prec, batch, ctx0, n_ctx=16, sd=None, focal_alpha=None, position="end",
+               csc=False):
     """The CoOp configuration of oracle/make_golden.py:run_coop (16 generic context tokens, seeded ctx from the fixture)."""
     from psrc_b200 import synthetic as S
     from psrc_b200.step import PromptedClipStep, StepConfig
@@ -100,7 +101,8 @@ def coop_setup(arch_name, tokens, device, prec, batch, ctx0, n_ctx=16, sd=None, 
     sd = sd if sd is not None else S.make_clip_state_dict(arch, seed=0)
     tokens = torch.as_tensor(np.asarray(tokens)).long()
     cfg = StepConfig(arch=arch, n_cls=tokens.shape[0], batch=batch, prec=prec, n_ctx_text=n_ctx, n_ctx_vision=0,
-                     depth_text=1, depth_vision=0, focal_alpha=focal_alpha, class_token_position=position)
+                     depth_text=1, depth_vision=0, focal_alpha=focal_alpha, class_token_position=position,
+                     ctx_per_class=csc)
     step = PromptedClipStep(cfg, sd, tokens, device)
     with torch.no_grad():
         step.params["ctx"].copy_(torch.as_tensor(ctx0))

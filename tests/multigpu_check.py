@@ -28,6 +28,8 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="images per rank")
     ap.add_argument("--prec", default="fp32")
     ap.add_argument("--arch", default="ViT-B/16")
+    ap.add_argument("--golden", default="", help="also compare the sharded step with this tests/golden fixture "
+                                                  "(cfg3_promptsrc_ce: global batch 128 / world images per rank)")
     args = ap.parse_args()
     world, rank, local = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -35,8 +37,15 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     from psrc_b200 import synthetic as S
     arch = S.ARCHS[args.arch]
+    fx = None
+    if args.golden:
+        from helpers import load_golden, ref_name
+        fx = load_golden(args.golden)
+        args.classes = fx["tokens"].shape[0]
+        assert fx["label"].shape[0] % world == 0 and not int(fx["focal"])
+        args.batch = fx["label"].shape[0] // world
     C = args.classes - args.classes % world
-    tokens = S.load_token_fixture()[:C]
+    tokens = S.load_token_fixture()[:C] if fx is None else fx["tokens"]
     Bg = args.batch * world
     image, label = S.synthetic_batch(Bg, C, arch.image_resolution, seed=1)
     depth = 9 if args.arch != "tiny" else 3
@@ -69,6 +78,16 @@ def main():
              "logits_maxabs": float((step.logits - ref.logits[:args.batch]).abs().max())}
         tol = dict(loss=1e-4, cos=0.99999, t=1e-5) if args.prec == "fp32" else dict(loss=5e-3, cos=0.9995, t=5e-3)
         ok = (m["losses_maxabs"] < tol["loss"] and m["grad_cos"] > tol["cos"] and m["t_hat_maxabs"] < tol["t"])
+        if fx is not None:   # the N-GPU step against the oracle / reference outputs of the whole batch
+            m["golden"] = args.golden
+            m["golden_loss_rel"] = abs(m["loss_sharded"] - float(fx["loss"])) / abs(float(fx["loss"]))
+            m["golden_logits_maxabs"] = float((step.logits.cpu() - torch.from_numpy(fx["logits"][:args.batch])).abs().max())
+            cs = {k: cos(step.grads[k], fx["grad/" + ref_name(k)]) for k in step.params}
+            m["golden_gradcos_worst"] = min(cs.values())
+            m["golden_gradcos_worst_key"] = min(cs, key=cs.get)
+            gt = dict(loss=1e-5, logits=1e-4, cos=0.9999) if args.prec == "fp32" else dict(loss=1e-2, logits=2e-2, cos=0.999)
+            ok = ok and m["golden_loss_rel"] < gt["loss"] and m["golden_logits_maxabs"] < gt["logits"] \
+                and m["golden_gradcos_worst"] >= gt["cos"]
         m["ok"] = ok
         line = json.dumps(m)
         print(line, flush=True)
