@@ -62,7 +62,7 @@ def flip_param(p: float = 0.5) -> bool:
     return bool(torch.rand(1) < p)
 
 
-def test_geometry(height: int, width: int, size: int):
+def eval_geometry(height: int, width: int, size: int):
     """Resize(size) on the smaller edge followed by CenterCrop(size) (transforms.py:337-341) as resampling geometry:
     returns (new_h, new_w, crop_top, crop_left) in the resized image."""
     if height <= width:
@@ -126,7 +126,7 @@ class DeviceTransform:
             win = arr[top:top + h, left:left + w]
             sx, sy, ox, oy = w / R, h / R, 0.0, 0.0
         else:
-            new_h, new_w, ct, cl = test_geometry(H, W, R)
+            new_h, new_w, ct, cl = eval_geometry(H, W, R)
             sx, sy = W / new_w, H / new_h
             mx, my = 2.0 * max(sx, 1.0) + 1.0, 2.0 * max(sy, 1.0) + 1.0      # bicubic support margin
             x0, x1 = max(0, int(cl * sx - mx)), min(W, int(math.ceil((cl + R) * sx + mx)))
@@ -148,39 +148,53 @@ class DeviceTransform:
 
 class DevicePreprocessor:
     """Device half: pinned-host uint8 canvases -> H2D on a copy stream -> `psrc_crop_resize_normalize` into the step's
-    fp32 image buffer.  Buffers are allocated once (graph-friendly); `stage()` may be called for batch i+1 while step i
-    computes (same look-ahead contract as `PromptedClipStep.stage_host`)."""
+    fp32 image buffer.  Buffers are allocated once; `stage()` may be called for batch i+1 as soon as batch i's kernel
+    has been launched (it waits for that kernel only, not for the step that follows it) -- the same look-ahead contract
+    as `PromptedClipStep.stage_host`."""
 
-    def __init__(self, device, batch, size=224, canvas=(256, 256), interpolation="bicubic", quantize=1,
+    def __init__(self, device, batch, size=224, canvas=(256, 256), interpolation="bicubic", quantize=2,
                  mean=CLIP_MEAN, std=CLIP_STD):
         self.device, self.batch, self.size = torch.device(device), batch, size
         self.interp, self.quantize, self.mean, self.std = INTERPOLATION[interpolation], int(quantize), mean, std
         self.u8 = torch.empty(batch, canvas[0], canvas[1], 3, dtype=torch.uint8, device=self.device)
         self.geom_f = torch.empty(batch, 4, dtype=torch.float32, device=self.device)
         self.geom_i = torch.empty(batch, 5, dtype=torch.int32, device=self.device)
+        self.labels = torch.empty(batch, dtype=torch.int32, device=self.device)
         self.taps = 0
-        self._copy, self._ready = None, None
+        self._copy, self._ready, self._consumed = None, None, None
+        self.staged_key = None
 
     def bytes_per_batch(self) -> int:
-        return self.u8.numel() + self.geom_f.numel() * 4 + self.geom_i.numel() * 4
+        return self.u8.numel() + self.geom_f.numel() * 4 + self.geom_i.numel() * 4 + self.labels.numel() * 8
 
-    def stage(self, item: dict):
+    def stage(self, item: dict, label_host=None):
         """Start the H2D copies of one collated batch ({"u8", "geom_f", "geom_i"}, pinned for true overlap)."""
         if self._copy is None:
             self._copy, self._ready = torch.cuda.Stream(device=self.device), torch.cuda.Event()
         self.taps = max_taps(item["geom_f"].numpy(), self.interp)
-        self._copy.wait_stream(torch.cuda.current_stream())      # the previous kernel has consumed the buffers
+        if self._consumed is not None:
+            self._copy.wait_event(self._consumed)                # the previous batch has left the staging buffers
         with torch.cuda.stream(self._copy):
             self.u8.copy_(item["u8"], non_blocking=True)
             self.geom_f.copy_(item["geom_f"], non_blocking=True)
             self.geom_i.copy_(item["geom_i"], non_blocking=True)
+            if label_host is not None:
+                self.labels.copy_(label_host.to(torch.int32), non_blocking=True)
             self._ready.record(self._copy)
+        self.staged_key = id(item["u8"])
 
-    def run(self, item: dict | None, out: torch.Tensor):
+    def run(self, item: dict | None, out: torch.Tensor, labels_out: torch.Tensor | None = None, label_host=None):
         """Resample the staged (or given) batch into `out` [B, 3, R, R] fp32 on the current stream."""
-        if item is not None:
-            self.stage(item)
-        torch.cuda.current_stream().wait_event(self._ready)
+        if item is not None and self.staged_key != id(item["u8"]):
+            self.stage(item, label_host)
+        main = torch.cuda.current_stream()
+        main.wait_event(self._ready)
         ops.crop_resize_normalize(self.u8, self.geom_f, self.geom_i, out, self.interp, self.quantize, self.taps,
                                   self.mean, self.std)
+        if labels_out is not None:
+            labels_out.copy_(self.labels, non_blocking=True)
+        if self._consumed is None:
+            self._consumed = torch.cuda.Event()
+        self._consumed.record(main)
+        self.staged_key = None
         return out

@@ -713,6 +713,24 @@ class PromptedClipStep:
             self.stage_host(*next_host)
         return self.loss_value()                                            # :330 (16-byte D2H)
 
+    def train_step_host_u8(self, item: dict, label_host: torch.Tensor, next_host=None, canvas=None) -> float:
+        """`train_step_host` fed by the on-device input pipeline (input_pipeline.DeviceTransform /
+        DevicePreprocessor): `item` = collated {"u8" [B,Hc,Wc,3] uint8, "geom_f" [B,4], "geom_i" [B,5]} from pinned host
+        memory (the crop boxes / flips were drawn on the host with the reference's RNG calls), label_host int64 [B].
+        H2D of the uint8 windows (a third of the fp32 batch at 256 x 256 canvases) -> crop / bicubic resample / flip /
+        normalise kernel into self.image -> step -> SGD -> loss.  `next_host = (item, labels)` starts the following
+        batch's copies under this step's compute."""
+        pre = getattr(self, "_pre", None)
+        if pre is None:
+            from .input_pipeline import DevicePreprocessor
+            pre = self._pre = DevicePreprocessor(self.device, self.cfg.batch, self.cfg.arch.image_resolution,
+                                                 canvas=canvas or tuple(item["u8"].shape[1:3]))
+        pre.run(item, self.image, labels_out=self.labels, label_host=label_host)
+        self.run()
+        if next_host is not None:
+            pre.stage(*next_host)
+        return self.loss_value()
+
     def stage_host(self, image_host: torch.Tensor, label_host: torch.Tensor):
         """Start the H2D copy of the NEXT batch into staging buffers on the copy stream and return at once."""
         cs = getattr(self, "_copy_stream", None)
