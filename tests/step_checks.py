@@ -60,7 +60,9 @@ def run_promptsrc_case(name: str, prec: str, sgd: bool = True) -> dict:
         m["fixed_embeddings_rel"] = float((fixed.cpu() - g("fixed_embeddings")).norm() / g("fixed_embeddings").norm())
         m["text_feat_maxabs"] = float((step.t_hat.cpu() - g("text_features")).abs().max())
     m["logits_maxabs"] = float((step.logits.cpu() - g("logits")).abs().max())
-    m["zs_logits_maxabs"] = float((step.zs_logits.cpu() - g("zs_logits")).abs().max())
+    dz = (step.zs_logits.cpu() - g("zs_logits")).abs()
+    m["zs_logits_maxabs"] = float(dz.max())
+    m["zs_logits_frac_over_1e-4"] = float((dz > 1e-4).float().mean())
     m["image_feat_maxabs"] = float((step.f_hat.cpu() - g("image_features")).abs().max())
     m["zs_image_feat_maxabs"] = float((step.zf_hat.cpu() - g("zs_image_features")).abs().max())
     loss = float(step.losses.sum())
@@ -69,7 +71,9 @@ def run_promptsrc_case(name: str, prec: str, sgd: bool = True) -> dict:
     m["ce_rel"] = abs(float(step.losses[0]) - float(fx["ce"])) / abs(float(fx["ce"]))
     if "loss_terms" in fx:                 # ce, kl, 25 * L1(text), 10 * L1(image): each term on its own
         ours, ref = step.losses.cpu().numpy(), fx["loss_terms"]
-        m["loss_terms_rel_max"] = float(np.max(np.abs(ours - ref) / np.maximum(np.abs(ref), 1e-12)))
+        rel = np.abs(ours - ref) / np.maximum(np.abs(ref), 1e-12)
+        m["loss_terms_rel_max"] = float(np.max(rel[[0, 2, 3]]))
+        m["kl_term_rel"] = float(rel[1])
     m.update(_argmax_metrics(step.logits, g("logits"), fx["argmax"], m["logits_maxabs"]))
     worst, worst_key = 2.0, None
     for k in step.params:
@@ -342,7 +346,17 @@ def check(m: dict, prec: str, name: str = "") -> list[str]:
     bad = []
     if m["logits_maxabs"] > t["logits"]:
         bad.append(f"logits max|d| {m['logits_maxabs']:.3e} > {t['logits']}")
-    if m["zs_logits_maxabs"] > t["logits"]:
+    if prec == "fp32":
+        # The teacher logits are s * f_zs . half(t_fixed) (promptsrc.py:201): the reference's own fp16 round trip of the
+        # init-time teacher text features is a discontinuity -- where our fp32 value and the reference's (equal to
+        # ~1e-7 relative) straddle an fp16 rounding boundary (probability ~2^-13 per element, i.e. a few dozen of the
+        # 512 000 elements at C = 1000) that element moves by one fp16 ulp (2^-15 .. 2^-14 at |t| ~ 0.03 .. 0.1) and the
+        # logits of that class by up to s * |f| * ulp = 100 * 0.15 * 6.1e-5 = 9e-4.  So: 1e-4 everywhere except an
+        # isolated <= 0.2 % of the entries, which stay below 1e-3.
+        if m["zs_logits_maxabs"] > 1e-3 or m["zs_logits_frac_over_1e-4"] > 2e-3:
+            bad.append(f"zs_logits max|d| {m['zs_logits_maxabs']:.3e} (limit 1e-3), fraction over 1e-4 "
+                       f"{m['zs_logits_frac_over_1e-4']:.2e} (limit 2e-3)")
+    elif m["zs_logits_maxabs"] > t["logits"]:
         bad.append(f"zs_logits max|d| {m['zs_logits_maxabs']:.3e} > {t['logits']}")
     for k in ("text_feat_maxabs", "image_feat_maxabs", "zs_image_feat_maxabs"):
         if m[k] > t["feat"]:
@@ -351,6 +365,10 @@ def check(m: dict, prec: str, name: str = "") -> list[str]:
         bad.append(f"loss rel {m['loss_rel']:.3e} > {t['loss']}")
     if m.get("loss_terms_rel_max", 0.0) > t["loss"]:
         bad.append(f"loss term rel {m['loss_terms_rel_max']:.3e} > {t['loss']}")
+    # the KL term compares the logits with the teacher logits and inherits their fp16 rounding flips (see above): a
+    # flipped class moves log-softmax of its column by ~1e-4 -- 5x the fp32 loss tolerance for this term only
+    if m.get("kl_term_rel", 0.0) > 5 * t["loss"]:
+        bad.append(f"KL term rel {m['kl_term_rel']:.3e} > {5 * t['loss']}")
     if m["gradcos_worst"] < t["cos"]:
         bad.append(f"grad cosine {m['gradcos_worst']:.6f} ({m['gradcos_worst_key']}) < {t['cos']}")
     if m["gradcos_all"] < t["cos_all"]:
