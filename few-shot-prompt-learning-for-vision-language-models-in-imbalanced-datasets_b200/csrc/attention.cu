@@ -17,9 +17,10 @@ int attn_fwd_small(const void* qkv, void* out, float* lse, int act_dtype, int n_
 int attn_bwd_small(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int act_dtype,
                    int grad_dtype, int n_seq, int L, int H, int causal, cudaStream_t s);
 bool attn_small_mma_supported(int L);
-int attn_fwd_small_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s);
-int attn_bwd_small_mma(const void* qkv, const void* dout, const float* lse, void* dqkv, int n_seq, int L, int H,
-                       int causal, cudaStream_t s);
+int attn_fwd_small_mma(const void* qkv, void* out, float* lse, int dtype, int n_seq, int L, int H, int causal,
+                       cudaStream_t s);
+int attn_bwd_small_mma(const void* qkv, const void* dout, const float* lse, void* dqkv, int qkv_dtype, int n_seq, int L,
+                       int H, int causal, cudaStream_t s);
 int attn_fwd_tc(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s);
 int attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int n_seq,
                 int L, int H, int causal, cudaStream_t s);
@@ -40,14 +41,19 @@ extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, 
                              int causal, int backend, psrc_stream_t stream) {
   PSRC_CHECK_ARG(qkv && out && lse, "psrc_attn_fwd: null pointer");
   PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && H > 0, "psrc_attn_fwd: bad shape n_seq=%d L=%d H=%d", n_seq, L, H);
-  PSRC_CHECK_ARG(dtype == PSRC_F32 || dtype == PSRC_BF16, "psrc_attn_fwd: bad dtype");
+  PSRC_CHECK_ARG(dtype >= PSRC_F32 && dtype <= PSRC_F16, "psrc_attn_fwd: bad dtype");
   if (n_seq == 0) return PSRC_OK;
+  if (dtype == PSRC_F16) {   // fp16 forward operands: the short-sequence tile kernels only (the truncated text tower)
+    PSRC_CHECK_ARG((backend == 0 || backend == 5) && al16(qkv) && al16(out) && attn_small_mma_supported(L),
+                   "psrc_attn_fwd: fp16 needs the mma.sync tile backend, aligned pointers and L <= 32 (L=%d)", L);
+    return attn_fwd_small_mma(qkv, out, lse, dtype, n_seq, L, H, causal, as_stream(stream));
+  }
   if (backend == 0)
     backend = (dtype == PSRC_BF16 && al16(qkv) && al16(out)) ? auto_backend(L) : 1;
   if (backend == 5) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out) && attn_small_mma_supported(L),
                    "psrc_attn_fwd: mma.sync tile backend needs aligned bf16 and L <= 32 (L=%d)", L);
-    return attn_fwd_small_mma(qkv, out, lse, n_seq, L, H, causal, as_stream(stream));
+    return attn_fwd_small_mma(qkv, out, lse, dtype, n_seq, L, H, causal, as_stream(stream));
   }
   if (backend == 4) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out) && attn_small_supported(L),
@@ -70,15 +76,20 @@ extern "C" int psrc_attn_bwd(const void* qkv, const void* out, const void* dout,
                              int dtype, int n_seq, int L, int H, int causal, int backend, psrc_stream_t stream) {
   PSRC_CHECK_ARG(qkv && out && dout && lse && dqkv, "psrc_attn_bwd: null pointer");
   PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && H > 0, "psrc_attn_bwd: bad shape n_seq=%d L=%d H=%d", n_seq, L, H);
-  PSRC_CHECK_ARG(dtype == PSRC_F32 || dtype == PSRC_BF16, "psrc_attn_bwd: bad dtype");
+  PSRC_CHECK_ARG(dtype >= PSRC_F32 && dtype <= PSRC_F16, "psrc_attn_bwd: bad dtype");
   if (n_seq == 0) return PSRC_OK;
   const bool ok16 = al16(qkv) && al16(out) && al16(dout) && al16(dqkv);
+  if (dtype == PSRC_F16) {   // qkv / out are fp16 (forward operands); dout / dqkv are bf16
+    PSRC_CHECK_ARG((backend == 0 || backend == 5) && ok16 && attn_small_mma_supported(L),
+                   "psrc_attn_bwd: fp16 needs the mma.sync tile backend, aligned pointers and L <= 32 (L=%d)", L);
+    return attn_bwd_small_mma(qkv, dout, lse, dqkv, dtype, n_seq, L, H, causal, as_stream(stream));
+  }
   if (backend == 0)
     backend = (dtype == PSRC_BF16 && ok16) ? auto_backend(L) : 1;
   if (backend == 5) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16 && attn_small_mma_supported(L),
                    "psrc_attn_bwd: mma.sync tile backend needs aligned bf16 and L <= 32 (L=%d)", L);
-    return attn_bwd_small_mma(qkv, dout, lse, dqkv, n_seq, L, H, causal, as_stream(stream));
+    return attn_bwd_small_mma(qkv, dout, lse, dqkv, dtype, n_seq, L, H, causal, as_stream(stream));
   }
   if (backend == 4) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16 && attn_small_supported(L),

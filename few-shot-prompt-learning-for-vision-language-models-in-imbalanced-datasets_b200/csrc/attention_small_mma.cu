@@ -24,9 +24,16 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// F16 = true: fp16 forward operands (q, k, v, P, O in IEEE half; 3 more mantissa bits than bf16 at the same rate)
+template <bool F16 = false>
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&v);
+  if constexpr (F16) {
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+  } else {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+  }
 }
 __device__ __forceinline__ void ldsm4(uint32_t (&r)[4], const __nv_bfloat16* p) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
@@ -38,10 +45,35 @@ __device__ __forceinline__ void ldsm4t(uint32_t (&r)[4], const __nv_bfloat16* p)
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                : "r"(smem_u32(p)));
 }
+template <bool F16 = false>
 __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  if constexpr (F16) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  } else {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+}
+// a staged [rows][kLd] tile of fp16 values -> bf16 in place (each lane converts the 16-byte chunks it staged).  The
+// backward's gradient contractions pair q / k / v with bf16 gradients; mma.sync wants one 16-bit format per instruction
+template <int ROWS>
+__device__ __forceinline__ void tile_f16_to_bf16(__nv_bfloat16* tile, int lane) {
+#pragma unroll
+  for (int i = 0; i < ROWS / 4; ++i) {
+    const int idx = lane + 32 * i, r = idx >> 3, c = idx & 7;
+    uint4 u = *reinterpret_cast<uint4*>(tile + r * 72 + c * 8);
+    uint32_t* w = reinterpret_cast<uint32_t*>(&u);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = __half22float2(*reinterpret_cast<__half2*>(&w[j]));
+      __nv_bfloat162 b = __floats2bfloat162_rn(f.x, f.y);
+      w[j] = *reinterpret_cast<uint32_t*>(&b);
+    }
+    *reinterpret_cast<uint4*>(tile + r * 72 + c * 8) = u;
+  }
 }
 
 // stage L rows of 64 bf16 (row stride `ld` elements in global) into a [16][kLd] tile, zero-filling rows >= L
@@ -66,16 +98,18 @@ __device__ __forceinline__ void unstage_tile(const __nv_bfloat16* tile, __nv_bfl
   }
 }
 // accumulator fragments of a [16 x 64] result (8 n-tiles) -> bf16 tile, scaled
+template <bool F16 = false>
 __device__ __forceinline__ void frags_to_tile(__nv_bfloat16* tile, const float (&c)[8][4], float s0, float s1,
                                               int g, int t) {
 #pragma unroll
   for (int n = 0; n < 8; ++n) {
-    *reinterpret_cast<uint32_t*>(tile + g * kLd + n * 8 + 2 * t) = pack_bf16(c[n][0] * s0, c[n][1] * s0);
-    *reinterpret_cast<uint32_t*>(tile + (g + 8) * kLd + n * 8 + 2 * t) = pack_bf16(c[n][2] * s1, c[n][3] * s1);
+    *reinterpret_cast<uint32_t*>(tile + g * kLd + n * 8 + 2 * t) = pack_bf16<F16>(c[n][0] * s0, c[n][1] * s0);
+    *reinterpret_cast<uint32_t*>(tile + (g + 8) * kLd + n * 8 + 2 * t) = pack_bf16<F16>(c[n][2] * s1, c[n][3] * s1);
   }
 }
 
 // C[16 x 16] = A[16 x 64] . B[16 x 64]^T, both tiles row-major [row][64]  (Q K^T, dO V^T)
+template <bool F16 = false>
 __device__ __forceinline__ void mma_abt(float (&c)[2][4], const __nv_bfloat16* A, const __nv_bfloat16* B, int lane) {
   const int arow = (lane & 7) + ((lane >> 3) & 1) * 8, acol = (lane >> 4) * 8;
   const int brow = lane & 7, bcol = (lane >> 3) * 8;
@@ -92,12 +126,13 @@ __device__ __forceinline__ void mma_abt(float (&c)[2][4], const __nv_bfloat16* A
     ldsm4(b[1], B + (8 + brow) * kLd + kk * 16 + bcol);    // n-tile 1
 #pragma unroll
     for (int n = 0; n < 2; ++n) {
-      mma16816(c[n], a0, b[n][0], b[n][1]);
-      mma16816(c[n], a1, b[n][2], b[n][3]);
+      mma16816<F16>(c[n], a0, b[n][0], b[n][1]);
+      mma16816<F16>(c[n], a1, b[n][2], b[n][3]);
     }
   }
 }
 // C[16 x 64] = A[16 x 16] . B[16 x 64], A given as a register fragment, B tile row-major [k][64]  (P V, dS K, ...)
+template <bool F16 = false>
 __device__ __forceinline__ void mma_ab(float (&c)[8][4], const uint32_t (&a)[4], const __nv_bfloat16* B, int lane) {
   const int brow = (lane & 7) + ((lane >> 3) & 1) * 8, bcol = (lane >> 4) * 8;
 #pragma unroll
@@ -106,12 +141,12 @@ __device__ __forceinline__ void mma_ab(float (&c)[8][4], const uint32_t (&a)[4],
     ldsm4t(b, B + brow * kLd + n * 8 + bcol);
 #pragma unroll
     for (int i = 0; i < 4; ++i) c[n][i] = c[n + 1][i] = 0.f;
-    mma16816(c[n], a, b[0], b[1]);
-    mma16816(c[n + 1], a, b[2], b[3]);
+    mma16816<F16>(c[n], a, b[0], b[1]);
+    mma16816<F16>(c[n + 1], a, b[2], b[3]);
   }
 }
 
-template <bool kCausal>
+template <bool kCausal, bool kF16>
 __global__ void __launch_bounds__(kWarps * 32)
 attn_small_mma_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
                           float* __restrict__ lse, int n_prob, int L, int H) {
@@ -129,7 +164,7 @@ attn_small_mma_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* 
   __syncwarp();
   const int g = lane >> 2, t = lane & 3;
   float s[2][4];
-  mma_abt(s, Qs, Ks, lane);
+  mma_abt<kF16>(s, Qs, Ks, lane);
   // scores -> log2 domain, mask (key >= L, causal key > query)
   float m0 = -INFINITY, m1 = -INFINITY;
 #pragma unroll
@@ -157,12 +192,12 @@ attn_small_mma_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* 
   sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
   sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1);
   sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
-  uint32_t p[4] = {pack_bf16(s[0][0], s[0][1]), pack_bf16(s[0][2], s[0][3]), pack_bf16(s[1][0], s[1][1]),
-                   pack_bf16(s[1][2], s[1][3])};
+  uint32_t p[4] = {pack_bf16<kF16>(s[0][0], s[0][1]), pack_bf16<kF16>(s[0][2], s[0][3]), pack_bf16<kF16>(s[1][0], s[1][1]),
+                   pack_bf16<kF16>(s[1][2], s[1][3])};
   float o[8][4];
-  mma_ab(o, p, Vs, lane);
+  mma_ab<kF16>(o, p, Vs, lane);
   __syncwarp();                       // every lane is done reading Qs (mma_abt) before it is reused for O
-  frags_to_tile(Qs, o, 1.f / sum0, 1.f / sum1, g, t);
+  frags_to_tile<kF16>(Qs, o, 1.f / sum0, 1.f / sum1, g, t);
   __syncwarp();
   unstage_tile(Qs, out + (long long)seq * L * D + h * 64, (long long)D, L, lane);
   if (t == 0) {
@@ -177,7 +212,7 @@ struct BwdSmem {
   __nv_bfloat16 p[16 * kXLd], ds[16 * kXLd];
 };
 
-template <bool kCausal>
+template <bool kCausal, bool kF16>
 __global__ void __launch_bounds__(kWarps * 32)
 attn_small_mma_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
                           const float* __restrict__ lse, __nv_bfloat16* __restrict__ dqkv, int n_prob, int L, int H) {
@@ -198,7 +233,14 @@ attn_small_mma_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bflo
   const float l0 = (g < L) ? lrow[g] * kLog2e : 0.f, l1 = (g + 8 < L) ? lrow[g + 8] * kLog2e : 0.f;
   __syncwarp();
   float s[2][4], dp[2][4];
-  mma_abt(s, S.q, S.k, lane);
+  mma_abt<kF16>(s, S.q, S.k, lane);         // the scores exactly as the forward computed them
+  if (kF16) {                                // gradient contractions run in bf16 (dO, dS are bf16)
+    __syncwarp();
+    tile_f16_to_bf16<16>(S.q, lane);
+    tile_f16_to_bf16<16>(S.k, lane);
+    tile_f16_to_bf16<16>(S.v, lane);
+    __syncwarp();
+  }
   mma_abt(dp, S.d, S.v, lane);
   float del0 = 0.f, del1 = 0.f;
 #pragma unroll
@@ -282,7 +324,7 @@ __device__ __forceinline__ void unstage_rows16(const __nv_bfloat16* tile16, __nv
   }
 }
 // C[16 x 8*NT] = A[16 x 64] . B[8*NT x 64]^T  (A, B: pointers to the first row of the operand inside a staged tile)
-template <int NT>
+template <int NT, bool F16 = false>
 __device__ __forceinline__ void mma_abt_n(float (&c)[NT][4], const __nv_bfloat16* A, const __nv_bfloat16* B, int lane) {
   const int arow = (lane & 7) + ((lane >> 3) & 1) * 8, acol = (lane >> 4) * 8;
   const int brow = lane & 7, bcol = (lane >> 3) * 8;
@@ -299,20 +341,21 @@ __device__ __forceinline__ void mma_abt_n(float (&c)[NT][4], const __nv_bfloat16
     for (int n = 0; n < NT; ++n) {
       uint32_t b[4];
       ldsm4(b, B + (8 * n + brow) * kLd + kk * 16 + bcol);
-      mma16816(c[n], a0, b[0], b[1]);
-      mma16816(c[n], a1, b[2], b[3]);
+      mma16816<F16>(c[n], a0, b[0], b[1]);
+      mma16816<F16>(c[n], a1, b[2], b[3]);
     }
   }
 }
 // C[16 x 64] += A[16 x 16] . B[16 x 64]  (B: pointer to the first of the 16 k-rows)
+template <bool F16 = false>
 __device__ __forceinline__ void mma_ab_acc(float (&c)[8][4], const uint32_t (&a)[4], const __nv_bfloat16* B, int lane) {
   const int brow = (lane & 7) + ((lane >> 3) & 1) * 8, bcol = (lane >> 4) * 8;
 #pragma unroll
   for (int n = 0; n < 8; n += 2) {
     uint32_t b[4];
     ldsm4t(b, B + brow * kLd + n * 8 + bcol);
-    mma16816(c[n], a, b[0], b[1]);
-    mma16816(c[n + 1], a, b[2], b[3]);
+    mma16816<F16>(c[n], a, b[0], b[1]);
+    mma16816<F16>(c[n + 1], a, b[2], b[3]);
   }
 }
 __device__ __forceinline__ void zero_acc(float (&c)[8][4]) {
@@ -335,7 +378,7 @@ struct FwdSmem2 {
   __nv_bfloat16 q[kR2 * kLd], k[kR2 * kLd], v[kR2 * kLd];
 };
 
-template <bool kCausal>
+template <bool kCausal, bool kF16>
 __global__ void __launch_bounds__(kWarps2 * 32)
 attn_small_mma2_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
                            float* __restrict__ lse, int n_prob, int L, int H) {
@@ -356,7 +399,7 @@ attn_small_mma2_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16*
 #pragma unroll 1
   for (int qt = 0; qt < n_qt; ++qt) {
     float s[4][4];
-    mma_abt_n<4>(s, S.q + qt * 16 * kLd, S.k, lane);
+    mma_abt_n<4, kF16>(s, S.q + qt * 16 * kLd, S.k, lane);
     float m0 = -INFINITY, m1 = -INFINITY;
 #pragma unroll
     for (int n = 0; n < 4; ++n)
@@ -383,12 +426,12 @@ attn_small_mma2_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16*
     zero_acc(o);
 #pragma unroll
     for (int kt = 0; kt < 2; ++kt) {
-      const uint32_t p[4] = {pack_bf16(s[2 * kt][0], s[2 * kt][1]), pack_bf16(s[2 * kt][2], s[2 * kt][3]),
-                             pack_bf16(s[2 * kt + 1][0], s[2 * kt + 1][1]), pack_bf16(s[2 * kt + 1][2], s[2 * kt + 1][3])};
-      mma_ab_acc(o, p, S.v + kt * 16 * kLd, lane);
+      const uint32_t p[4] = {pack_bf16<kF16>(s[2 * kt][0], s[2 * kt][1]), pack_bf16<kF16>(s[2 * kt][2], s[2 * kt][3]),
+                             pack_bf16<kF16>(s[2 * kt + 1][0], s[2 * kt + 1][1]), pack_bf16<kF16>(s[2 * kt + 1][2], s[2 * kt + 1][3])};
+      mma_ab_acc<kF16>(o, p, S.v + kt * 16 * kLd, lane);
     }
     __syncwarp();                       // all lanes have read Q rows of this tile; they become the O staging rows
-    frags_to_tile(S.q + qt * 16 * kLd, o, 1.f / sum0, 1.f / sum1, g, t);
+    frags_to_tile<kF16>(S.q + qt * 16 * kLd, o, 1.f / sum0, 1.f / sum1, g, t);
     if (t == 0) {
       float* l = lse + ((long long)seq * H + h) * L;
       const int r0 = qt * 16 + g;
@@ -408,7 +451,7 @@ struct BwdSmem2 {
   __nv_bfloat16 stg[16 * kLd];
 };
 
-template <bool kCausal>
+template <bool kCausal, bool kF16>
 __global__ void __launch_bounds__(kWarps2 * 32)
 attn_small_mma2_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
                            const float* __restrict__ lse, __nv_bfloat16* __restrict__ dqkv, int n_prob, int L, int H) {
@@ -429,11 +472,30 @@ attn_small_mma2_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfl
   __nv_bfloat16* drow = dqkv + (long long)seq * L * ld + h * 64;
   const int n_t = (L + 15) >> 4;          // query tiles = key tiles
   __syncwarp();
+  // fp16 forward operands: the scores of both query tiles from the fp16 q / k (as the forward computed them), then
+  // q / k / v become bf16 in place for the gradient contractions
+  float s_all[2][4][4];
+  if (kF16) {
+#pragma unroll
+    for (int qt = 0; qt < 2; ++qt) mma_abt_n<4, true>(s_all[qt], S.q + qt * 16 * kLd, S.k, lane);
+    __syncwarp();
+    tile_f16_to_bf16<32>(S.q, lane);
+    tile_f16_to_bf16<32>(S.k, lane);
+    tile_f16_to_bf16<32>(S.v, lane);
+    __syncwarp();
+  }
   // ---- pass 1 (per query tile): P, dS into the shared tiles; dQ
-#pragma unroll 1
+#pragma unroll(kF16 ? 2 : 1)
   for (int qt = 0; qt < 2; ++qt) {
     float s[4][4], dp[4][4];
-    mma_abt_n<4>(s, S.q + qt * 16 * kLd, S.k, lane);
+    if (kF16) {
+#pragma unroll
+      for (int n = 0; n < 4; ++n)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) s[n][i] = s_all[qt][n][i];
+    } else {
+      mma_abt_n<4>(s, S.q + qt * 16 * kLd, S.k, lane);
+    }
     mma_abt_n<4>(dp, S.d + qt * 16 * kLd, S.v, lane);
     const int r0 = qt * 16 + g;
     const float l0 = (r0 < L) ? lrow[r0] * kLog2e : 0.f, l1 = (r0 + 8 < L) ? lrow[r0 + 8] * kLog2e : 0.f;
@@ -505,50 +567,63 @@ attn_small_mma2_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfl
 
 bool attn_small_mma_supported(int L) { return L >= 1 && L <= 32; }
 
-int attn_fwd_small_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H, int causal, cudaStream_t s) {
+int attn_fwd_small_mma(const void* qkv, void* out, float* lse, int dtype, int n_seq, int L, int H, int causal,
+                       cudaStream_t s) {
   using namespace asm2;
   const int n_prob = n_seq * H;
   const int grid = (n_prob + kWarps - 1) / kWarps;
-  const __nv_bfloat16* q = reinterpret_cast<const __nv_bfloat16*>(qkv);
+  const __nv_bfloat16* q = reinterpret_cast<const __nv_bfloat16*>(qkv);   // 16-bit storage; the format is kF16
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+  const bool f16 = dtype == PSRC_F16;
+#define PSRC_SM_PICK(KERNEL, ...)                                  \
+  do {                                                             \
+    if (causal && f16) KERNEL<true, true> __VA_ARGS__;             \
+    else if (causal) KERNEL<true, false> __VA_ARGS__;              \
+    else if (f16) KERNEL<false, true> __VA_ARGS__;                 \
+    else KERNEL<false, false> __VA_ARGS__;                         \
+  } while (0)
+#define PSRC_SM_ATTR(KERNEL, BYTES)                                                                              \
+  do {                                                                                                           \
+    PSRC_CHECK_CUDA(cudaFuncSetAttribute(KERNEL<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BYTES));   \
+    PSRC_CHECK_CUDA(cudaFuncSetAttribute(KERNEL<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BYTES));  \
+    PSRC_CHECK_CUDA(cudaFuncSetAttribute(KERNEL<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BYTES));  \
+    PSRC_CHECK_CUDA(cudaFuncSetAttribute(KERNEL<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BYTES)); \
+  } while (0)
   if (L > 16) {
     const int bytes = kWarps2 * (int)sizeof(FwdSmem2);
     static bool attr2 = false;
     if (!attr2) {
-      PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma2_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-      PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma2_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+      PSRC_SM_ATTR(attn_small_mma2_fwd_kernel, bytes);
       attr2 = true;
     }
     const int grid2 = (n_prob + kWarps2 - 1) / kWarps2;
-    if (causal) attn_small_mma2_fwd_kernel<true><<<grid2, kWarps2 * 32, bytes, s>>>(q, o, lse, n_prob, L, H);
-    else attn_small_mma2_fwd_kernel<false><<<grid2, kWarps2 * 32, bytes, s>>>(q, o, lse, n_prob, L, H);
+    PSRC_SM_PICK(attn_small_mma2_fwd_kernel, <<<grid2, kWarps2 * 32, bytes, s>>>(q, o, lse, n_prob, L, H));
     PSRC_CHECK_LAUNCH();
     return PSRC_OK;
   }
-  if (causal) attn_small_mma_fwd_kernel<true><<<grid, kWarps * 32, 0, s>>>(q, o, lse, n_prob, L, H);
-  else attn_small_mma_fwd_kernel<false><<<grid, kWarps * 32, 0, s>>>(q, o, lse, n_prob, L, H);
+  PSRC_SM_PICK(attn_small_mma_fwd_kernel, <<<grid, kWarps * 32, 0, s>>>(q, o, lse, n_prob, L, H));
   PSRC_CHECK_LAUNCH();
   return PSRC_OK;
 }
 
-int attn_bwd_small_mma(const void* qkv, const void* dout, const float* lse, void* dqkv, int n_seq, int L, int H,
-                       int causal, cudaStream_t s) {
+// qkv_dtype: PSRC_BF16 or PSRC_F16 (forward operands); dout / dqkv are always bf16
+int attn_bwd_small_mma(const void* qkv, const void* dout, const float* lse, void* dqkv, int qkv_dtype, int n_seq, int L,
+                       int H, int causal, cudaStream_t s) {
   using namespace asm2;
   const int n_prob = n_seq * H;
+  const bool f16 = qkv_dtype == PSRC_F16;
+  const __nv_bfloat16* q = reinterpret_cast<const __nv_bfloat16*>(qkv);
+  const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(dout);
+  __nv_bfloat16* dq = reinterpret_cast<__nv_bfloat16*>(dqkv);
   if (L > 16) {
     const int bytes2 = kWarps2 * (int)sizeof(BwdSmem2);
     static bool attr2 = false;
     if (!attr2) {
-      PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma2_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes2));
-      PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma2_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes2));
+      PSRC_SM_ATTR(attn_small_mma2_bwd_kernel, bytes2);
       attr2 = true;
     }
     const int grid2 = (n_prob + kWarps2 - 1) / kWarps2;
-    const __nv_bfloat16* q2 = reinterpret_cast<const __nv_bfloat16*>(qkv);
-    const __nv_bfloat16* d2 = reinterpret_cast<const __nv_bfloat16*>(dout);
-    __nv_bfloat16* dq2 = reinterpret_cast<__nv_bfloat16*>(dqkv);
-    if (causal) attn_small_mma2_bwd_kernel<true><<<grid2, kWarps2 * 32, bytes2, s>>>(q2, d2, lse, dq2, n_prob, L, H);
-    else attn_small_mma2_bwd_kernel<false><<<grid2, kWarps2 * 32, bytes2, s>>>(q2, d2, lse, dq2, n_prob, L, H);
+    PSRC_SM_PICK(attn_small_mma2_bwd_kernel, <<<grid2, kWarps2 * 32, bytes2, s>>>(q, d, lse, dq, n_prob, L, H));
     PSRC_CHECK_LAUNCH();
     return PSRC_OK;
   }
@@ -556,17 +631,14 @@ int attn_bwd_small_mma(const void* qkv, const void* dout, const float* lse, void
   const int bytes = kWarps * (int)sizeof(BwdSmem);
   static bool attr_set = false;
   if (!attr_set) {
-    PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-    PSRC_CHECK_CUDA(cudaFuncSetAttribute(attn_small_mma_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PSRC_SM_ATTR(attn_small_mma_bwd_kernel, bytes);
     attr_set = true;
   }
-  const __nv_bfloat16* q = reinterpret_cast<const __nv_bfloat16*>(qkv);
-  const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(dout);
-  __nv_bfloat16* dq = reinterpret_cast<__nv_bfloat16*>(dqkv);
-  if (causal) attn_small_mma_bwd_kernel<true><<<grid, kWarps * 32, bytes, s>>>(q, d, lse, dq, n_prob, L, H);
-  else attn_small_mma_bwd_kernel<false><<<grid, kWarps * 32, bytes, s>>>(q, d, lse, dq, n_prob, L, H);
+  PSRC_SM_PICK(attn_small_mma_bwd_kernel, <<<grid, kWarps * 32, bytes, s>>>(q, d, lse, dq, n_prob, L, H));
   PSRC_CHECK_LAUNCH();
   return PSRC_OK;
+#undef PSRC_SM_PICK
+#undef PSRC_SM_ATTR
 }
 
 }  // namespace psrc

@@ -44,11 +44,13 @@ static inline cudaStream_t as_stream(psrc_stream_t s) { return reinterpret_cast<
 // ---------------------------------------------------------------- dtype helpers
 __device__ __forceinline__ float to_f32(float v) { return v; }
 __device__ __forceinline__ float to_f32(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float to_f32(__half v) { return __half2float(v); }
 template <typename T> __device__ __forceinline__ T from_f32(float v);
 template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) {
   return __float2bfloat16_rn(v);
 }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
 // fp16 round trip of a prompt value: reference `.half()` then type-promotion back to fp32
 // (PromptSRC/clip/model.py:238,249,414)
 __device__ __forceinline__ float fp16_round(float v) { return __half2float(__float2half_rn(v)); }

@@ -19,7 +19,20 @@ struct EpiParams {
 
 __device__ __forceinline__ void load_row_chunk(const void* base, int dtype, long long ld, int row,
                                                int col0, float (&v)[32]) {
-  if (dtype == PSRC_BF16) {
+  if (dtype == PSRC_F16) {
+    const uint4* p = reinterpret_cast<const uint4*>(reinterpret_cast<const __half*>(base) + (long long)row * ld + col0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint4 u = p[i];
+      const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float2 f = __half22float2(h[j]);
+        v[i * 8 + j * 2] = f.x;
+        v[i * 8 + j * 2 + 1] = f.y;
+      }
+    }
+  } else if (dtype == PSRC_BF16) {
     const uint4* p = reinterpret_cast<const uint4*>(
         reinterpret_cast<const __nv_bfloat16*>(base) + (long long)row * ld + col0);
 #pragma unroll
@@ -46,7 +59,17 @@ __device__ __forceinline__ void load_row_chunk(const void* base, int dtype, long
 
 __device__ __forceinline__ void store_row_chunk(void* base, int dtype, long long ld, int row, int col0,
                                                 const float (&v)[32]) {
-  if (dtype == PSRC_BF16) {
+  if (dtype == PSRC_F16) {
+    uint4* p = reinterpret_cast<uint4*>(reinterpret_cast<__half*>(base) + (long long)row * ld + col0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint4 u;
+      __half2* h = reinterpret_cast<__half2*>(&u);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) h[j] = __floats2half2_rn(v[i * 8 + j * 2], v[i * 8 + j * 2 + 1]);
+      p[i] = u;
+    }
+  } else if (dtype == PSRC_BF16) {
     uint4* p = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(base) + (long long)row * ld + col0);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -64,11 +87,13 @@ __device__ __forceinline__ void store_row_chunk(void* base, int dtype, long long
 }
 
 __device__ __forceinline__ float load_elem(const void* base, int dtype, long long idx) {
+  if (dtype == PSRC_F16) return __half2float(reinterpret_cast<const __half*>(base)[idx]);
   return dtype == PSRC_BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[idx])
                             : reinterpret_cast<const float*>(base)[idx];
 }
 __device__ __forceinline__ void store_elem(void* base, int dtype, long long idx, float v) {
-  if (dtype == PSRC_BF16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16_rn(v);
+  if (dtype == PSRC_F16) reinterpret_cast<__half*>(base)[idx] = __float2half_rn(v);
+  else if (dtype == PSRC_BF16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16_rn(v);
   else reinterpret_cast<float*>(base)[idx] = v;
 }
 

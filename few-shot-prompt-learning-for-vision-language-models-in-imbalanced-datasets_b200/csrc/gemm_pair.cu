@@ -73,7 +73,23 @@ struct Params {
   const float* bias;
   float alpha;
   int has_out2;
+  // 16-bit formats (0 = bf16, 1 = fp16): A / W operands, the 16-bit output(s), the QuickGELU' aux operand.  fp16
+  // forward operands carry 3 more mantissa bits than bf16 at the same tensor-core rate ("fp16 forward")
+  int ab_f16, out_f16, out2_f16, aux_f16;
 };
+
+__device__ __forceinline__ uint32_t pack16(float lo, float hi, int f16) {
+  if (f16) {
+    __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+  }
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float2 unpack16(uint32_t u, int f16) {
+  if (f16) return __half22float2(*reinterpret_cast<__half2*>(&u));
+  return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
+}
 
 // 16-byte chunk j of row r inside a staging box whose rows are RB bytes (128 -> SWIZZLE_128B, 64 -> SWIZZLE_64B)
 template <int RB>
@@ -166,9 +182,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA, one thread) =====================
     if (rank == 0 && lane == 0) {
-      // instruction descriptor: D=f32, A=B=bf16, both K-major, N = BN, M = 256 (pair)
-      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
-                                 ((uint32_t)(256 >> 4) << 24);
+      // instruction descriptor: D=f32, A=B=bf16 (format 1) or fp16 (format 0), both K-major, N = BN, M = 256 (pair)
+      const uint32_t idesc = (1u << 4) | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10))) | ((uint32_t)(BN >> 3) << 17) |
+                             ((uint32_t)(256 >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
@@ -265,10 +281,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               const uint4 u = *reinterpret_cast<const uint4*>(in + sw_chunk<64>(r_cta, j));
-              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+              const uint32_t* h = reinterpret_cast<const uint32_t*>(&u);
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                const float2 f = __bfloat1622float2(h[e]);
+                const float2 f = unpack16(h[e], p.aux_f16);
                 v[8 * j + 2 * e] *= quickgelu_grad_fast(f.x);
                 v[8 * j + 2 * e + 1] *= quickgelu_grad_fast(f.y);
               }
@@ -285,9 +301,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               uint4 u;
-              __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+              uint32_t* h = reinterpret_cast<uint32_t*>(&u);
 #pragma unroll
-              for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[8 * j + 2 * e], v[8 * j + 2 * e + 1]);
+              for (int e = 0; e < 4; ++e) h[e] = pack16(v[8 * j + 2 * e], v[8 * j + 2 * e + 1], p.out2_f16);
               *reinterpret_cast<uint4*>(oslot + 2048 + sw_chunk<64>(lane, j)) = u;
             }
           }
@@ -303,9 +319,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 u;
-            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+            uint32_t* h = reinterpret_cast<uint32_t*>(&u);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[8 * j + 2 * e], v[8 * j + 2 * e + 1]);
+            for (int e = 0; e < 4; ++e) h[e] = pack16(v[8 * j + 2 * e], v[8 * j + 2 * e + 1], p.out_f16);
             *reinterpret_cast<uint4*>(oslot + sw_chunk<kOutRowBytes>(lane, j)) = u;
           }
         }
@@ -360,12 +376,14 @@ static int make_map(CUtensorMap* map, const void* base, int dtype, long long row
     set_error("cuTensorMapEncodeTiled entry point not available");
     return PSRC_ERR_CUDA;
   }
-  const int esz = dtype == PSRC_BF16 ? 2 : 4;
+  const int esz = dtype == PSRC_F32 ? 4 : 2;
   cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t gstride[1] = {(cuuint64_t)ld * esz};
   cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, dtype == PSRC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+  const CUtensorMapDataType tdt = dtype == PSRC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                  : dtype == PSRC_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  CUresult r = fn(map, tdt, 2,
                   const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -399,18 +417,18 @@ static int launch(const psrc_gemm_args& a, cudaStream_t stream) {
   }
   CUtensorMap ta, tw, to, to2, tin;
   int rc;
-  if ((rc = make_map(&ta, a.A, PSRC_BF16, a.M, a.K, a.lda, kBK, kBMcta, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
-  if ((rc = make_map(&tw, a.W, PSRC_BF16, a.N, a.K, a.ldw, kBK, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = make_map(&ta, a.A, a.ab_dtype, a.M, a.K, a.lda, kBK, kBMcta, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = make_map(&tw, a.W, a.ab_dtype, a.N, a.K, a.ldw, kBK, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   const CUtensorMapSwizzle osw = OUT_BYTES == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   if ((rc = make_map(&to, a.out, a.out_dtype, a.M, a.N, a.ldo, 32, 32, osw))) return rc;
   to2 = to;
   tin = to;
   if (MODE == kGelu && a.out2)
-    if ((rc = make_map(&to2, a.out2, PSRC_BF16, a.M, a.N, a.ldo2, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+    if ((rc = make_map(&to2, a.out2, a.out2_dtype, a.M, a.N, a.ldo2, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   if (MODE == kResidual)
     if ((rc = make_map(&tin, a.residual, PSRC_F32, a.M, a.N, a.ldres, 32, 128, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if (MODE == kGeluGrad)
-    if ((rc = make_map(&tin, a.aux, PSRC_BF16, a.M, a.N, a.ldaux, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+    if ((rc = make_map(&tin, a.aux, a.aux_dtype, a.M, a.N, a.ldaux, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   Params p;
   p.M = a.M; p.N = a.N; p.K = a.K;
   p.tiles_m = (a.M + 255) / 256;
@@ -418,6 +436,10 @@ static int launch(const psrc_gemm_args& a, cudaStream_t stream) {
   p.bias = a.bias;
   p.alpha = a.alpha;
   p.has_out2 = (MODE == kGelu && a.out2) ? 1 : 0;
+  p.ab_f16 = a.ab_dtype == PSRC_F16;
+  p.out_f16 = a.out_dtype == PSRC_F16;
+  p.out2_f16 = a.out2_dtype == PSRC_F16;
+  p.aux_f16 = a.aux_dtype == PSRC_F16;
   const int pairs = std::min(p.tiles_m * p.tiles_n, sm_count() / 2);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * pairs);
@@ -453,13 +475,13 @@ static int launch_bn(const psrc_gemm_args& a, cudaStream_t stream) {
 static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // which fused-epilogue combinations the CTA-pair kernel implements (everything the training step launches)
+static bool is16(int dtype) { return dtype == PSRC_BF16 || dtype == PSRC_F16; }
+
 static int pair_mode(const psrc_gemm_args& a) {
   if (a.act == PSRC_ACT_NONE && !a.residual && !a.out2) return pair::kNone;
-  if (a.act == PSRC_ACT_QUICKGELU && !a.residual && a.out_dtype == PSRC_BF16 &&
-      (!a.out2 || a.out2_dtype == PSRC_BF16))
+  if (a.act == PSRC_ACT_QUICKGELU && !a.residual && is16(a.out_dtype) && (!a.out2 || is16(a.out2_dtype)))
     return pair::kGelu;
-  if (a.act == PSRC_ACT_QUICKGELU_GRAD && !a.residual && !a.out2 && a.aux_dtype == PSRC_BF16 &&
-      a.out_dtype == PSRC_BF16)
+  if (a.act == PSRC_ACT_QUICKGELU_GRAD && !a.residual && !a.out2 && is16(a.aux_dtype) && is16(a.out_dtype))
     return pair::kGeluGrad;
   if (a.act == PSRC_ACT_NONE && a.residual && !a.out2 && a.out_dtype == PSRC_F32)
     return (a.residual == a.out && a.ldres == a.ldo) ? pair::kResidualInPlace : pair::kResidual;
@@ -470,7 +492,7 @@ bool gemm_pair_supported(const psrc_gemm_args& a) {
   if (!gemm_tc_supported(a) || pair_mode(a) < 0) return false;
   auto ok = [](const void* p, long long ld, int dtype) {
     if (!p) return true;
-    const int per16 = dtype == PSRC_BF16 ? 8 : 4;
+    const int per16 = dtype == PSRC_F32 ? 4 : 8;
     return al16(p) && (ld % per16 == 0);
   };
   return a.N % 8 == 0 && ok(a.bias, 4, PSRC_F32) && ok(a.aux, a.ldaux, a.aux_dtype) &&

@@ -145,7 +145,10 @@ static int gemm_simt(const psrc_gemm_args& a, cudaStream_t stream) {
   EpiParams epi;
   fill_epi(a, epi);
   dim3 grid((a.N + kTN - 1) / kTN, (a.M + kTM - 1) / kTM);
-  if (a.ab_dtype == PSRC_BF16) {
+  if (a.ab_dtype == PSRC_F16) {
+    gemm_simt_kernel<__half><<<grid, 256, 0, stream>>>(
+        reinterpret_cast<const __half*>(a.A), a.lda, reinterpret_cast<const __half*>(a.W), a.ldw, a.K, epi);
+  } else if (a.ab_dtype == PSRC_BF16) {
     gemm_simt_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(
         reinterpret_cast<const __nv_bfloat16*>(a.A), a.lda, reinterpret_cast<const __nv_bfloat16*>(a.W), a.ldw,
         a.K, epi);
@@ -166,8 +169,8 @@ extern "C" int psrc_gemm(const psrc_gemm_args* args, psrc_stream_t stream) {
   const psrc_gemm_args& a = *args;
   PSRC_CHECK_ARG(a.M >= 0 && a.N > 0 && a.K > 0, "psrc_gemm: bad shape M=%d N=%d K=%d", a.M, a.N, a.K);
   PSRC_CHECK_ARG(a.A && a.W && a.out, "psrc_gemm: null A/W/out");
-  PSRC_CHECK_ARG(a.ab_dtype == PSRC_F32 || a.ab_dtype == PSRC_BF16, "psrc_gemm: bad ab_dtype %d", a.ab_dtype);
-  PSRC_CHECK_ARG(a.out_dtype == PSRC_F32 || a.out_dtype == PSRC_BF16, "psrc_gemm: bad out_dtype");
+  PSRC_CHECK_ARG(a.ab_dtype >= PSRC_F32 && a.ab_dtype <= PSRC_F16, "psrc_gemm: bad ab_dtype %d", a.ab_dtype);
+  PSRC_CHECK_ARG(a.out_dtype >= PSRC_F32 && a.out_dtype <= PSRC_F16, "psrc_gemm: bad out_dtype");
   PSRC_CHECK_ARG(a.act >= PSRC_ACT_NONE && a.act <= PSRC_ACT_QUICKGELU_GRAD, "psrc_gemm: bad act %d", a.act);
   PSRC_CHECK_ARG(a.act != PSRC_ACT_QUICKGELU_GRAD || a.aux != nullptr, "psrc_gemm: QUICKGELU_GRAD needs aux");
   PSRC_CHECK_ARG(a.lda >= a.K && a.ldw >= a.K && a.ldo >= a.N, "psrc_gemm: leading dimension too small");
@@ -176,7 +179,7 @@ extern "C" int psrc_gemm(const psrc_gemm_args* args, psrc_stream_t stream) {
   if (backend == PSRC_GEMM_AUTO) backend = gemm_tc_supported(a) ? PSRC_GEMM_TCGEN05 : PSRC_GEMM_SIMT;
   if (backend == PSRC_GEMM_TCGEN05 || backend == PSRC_GEMM_TCGEN05_1CTA) {
     PSRC_CHECK_ARG(gemm_tc_supported(a),
-                   "psrc_gemm: tcgen05 backend needs bf16 A/W, K%%8==0, lda/ldw%%8==0, 16B-aligned pointers");
+                   "psrc_gemm: tcgen05 backend needs bf16 / fp16 A/W, K%%8==0, lda/ldw%%8==0, 16B-aligned pointers");
     if (backend == PSRC_GEMM_TCGEN05 && gemm_pair_supported(a)) return gemm_pair(a, as_stream(stream));
     return gemm_tc1(a, as_stream(stream));
   }

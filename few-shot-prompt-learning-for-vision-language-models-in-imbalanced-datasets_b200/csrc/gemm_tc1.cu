@@ -52,7 +52,7 @@ struct GemmSmem {
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-               int K, int tiles_m, int tiles_n, EpiParams epi) {
+               int K, int tiles_m, int tiles_n, int ab_f16, EpiParams epi) {
   using S = GemmSmem<BN, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -114,7 +114,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     // ===================== MMA issuer (one thread) =====================
     if (lane == 0) {
       // instruction descriptor: D=f32, A=B=bf16, both K-major, N = BN, M = 128
-      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
+      const uint32_t idesc = (1u << 4) | (ab_f16 ? 0u : ((1u << 7) | (1u << 10))) | ((uint32_t)(BN >> 3) << 17) |
                                  ((uint32_t)(kBM >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
@@ -201,7 +201,7 @@ static EncodeTiledFn get_encode_fn() {
 
 // rows x K bf16 row-major matrix (row stride ld elements) -> boxes of box_rows x 64, 128B swizzle
 static int make_tmap(CUtensorMap* map, const void* base, long long rows, long long K, long long ld,
-                     int box_rows) {
+                     int box_rows, int f16) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled entry point not available");
@@ -211,7 +211,8 @@ static int make_tmap(CUtensorMap* map, const void* base, long long rows, long lo
   cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
   cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box,
+  CUresult r = fn(map, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(base), gdim, gstride, box,
                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -243,13 +244,14 @@ static int launch_tc(const psrc_gemm_args& a, const EpiParams& epi, cudaStream_t
     attr_set = true;
   }
   CUtensorMap ta, tw;
-  int rc = make_tmap(&ta, a.A, a.M, a.K, a.lda, kBM);
+  const int f16 = a.ab_dtype == PSRC_F16;
+  int rc = make_tmap(&ta, a.A, a.M, a.K, a.lda, kBM, f16);
   if (rc) return rc;
-  rc = make_tmap(&tw, a.W, a.N, a.K, a.ldw, BN);
+  rc = make_tmap(&tw, a.W, a.N, a.K, a.ldw, BN, f16);
   if (rc) return rc;
   const int tiles_m = (a.M + kBM - 1) / kBM, tiles_n = (a.N + BN - 1) / BN;
   const int grid = std::min(tiles_m * tiles_n, num_sms());
-  gemm_tc_kernel<BN, STAGES><<<grid, kGemmThreads, S::kDynBytes, stream>>>(ta, tw, a.K, tiles_m, tiles_n, epi);
+  gemm_tc_kernel<BN, STAGES><<<grid, kGemmThreads, S::kDynBytes, stream>>>(ta, tw, a.K, tiles_m, tiles_n, f16, epi);
   PSRC_CHECK_LAUNCH();
   return PSRC_OK;
 }
@@ -257,7 +259,7 @@ static int launch_tc(const psrc_gemm_args& a, const EpiParams& epi, cudaStream_t
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 bool gemm_tc_supported(const psrc_gemm_args& a) {
-  return a.ab_dtype == PSRC_BF16 && a.K % 8 == 0 && a.lda % 8 == 0 && a.ldw % 8 == 0 && aligned16(a.A) &&
+  return (a.ab_dtype == PSRC_BF16 || a.ab_dtype == PSRC_F16) && a.K % 8 == 0 && a.lda % 8 == 0 && a.ldw % 8 == 0 && aligned16(a.A) &&
          aligned16(a.W) && a.M > 0 && a.N > 0 && a.K > 0;
 }
 
@@ -271,7 +273,7 @@ void fill_epi(const psrc_gemm_args& a, EpiParams& e) {
   e.alpha = a.alpha;
   auto ok = [](const void* p, long long ld, int dtype) {
     if (!p) return true;
-    int per16 = dtype == PSRC_BF16 ? 8 : 4;
+    int per16 = dtype == PSRC_F32 ? 4 : 8;
     return aligned16(p) && (ld % per16 == 0);
   };
   e.vec_ok = (a.N % 8 == 0) && ok(a.bias, 4, PSRC_F32) && ok(a.aux, a.ldaux, a.aux_dtype) &&

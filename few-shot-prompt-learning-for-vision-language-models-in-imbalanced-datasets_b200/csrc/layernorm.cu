@@ -25,6 +25,14 @@ __device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, float4 v
   u.y = *reinterpret_cast<uint32_t*>(&b);
   *reinterpret_cast<uint2*>(p) = u;
 }
+template <>
+__device__ __forceinline__ void store4<__half>(__half* p, float4 v) {
+  __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&a);
+  u.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = u;
+}
 template <typename T>
 __device__ __forceinline__ float4 load4(const T* p);
 template <>
@@ -247,6 +255,8 @@ extern "C" int psrc_layernorm_fwd(const float* x, const float* gamma, const floa
   CHECK_LN_COMMON("psrc_layernorm_fwd");
   PSRC_CHECK_ARG(x && gamma && beta && y, "psrc_layernorm_fwd: null pointer");
   if (rows == 0) return PSRC_OK;
+  if (out_dtype == PSRC_F16)
+    return launch_fwd<__half>(x, nullptr, 0, gamma, beta, y, mean, rstd, rows, D, eps, as_stream(stream));
   if (out_dtype == PSRC_BF16)
     return launch_fwd<__nv_bfloat16>(x, nullptr, 0, gamma, beta, y, mean, rstd, rows, D, eps, as_stream(stream));
   return launch_fwd<float>(x, nullptr, 0, gamma, beta, y, mean, rstd, rows, D, eps, as_stream(stream));
@@ -269,6 +279,8 @@ extern "C" int psrc_gather_ln_fwd(const float* x, const int32_t* idx, const floa
   CHECK_LN_COMMON("psrc_gather_ln_fwd");
   PSRC_CHECK_ARG(x && gamma && beta && y && L > 0, "psrc_gather_ln_fwd: bad arguments");
   if (rows == 0) return PSRC_OK;
+  if (out_dtype == PSRC_F16)
+    return launch_fwd<__half>(x, idx, L, gamma, beta, y, mean, rstd, rows, D, eps, as_stream(stream));
   if (out_dtype == PSRC_BF16)
     return launch_fwd<__nv_bfloat16>(x, idx, L, gamma, beta, y, mean, rstd, rows, D, eps, as_stream(stream));
   return launch_fwd<float>(x, idx, L, gamma, beta, y, mean, rstd, rows, D, eps, as_stream(stream));

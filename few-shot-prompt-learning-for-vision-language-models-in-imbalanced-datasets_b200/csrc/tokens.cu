@@ -4,6 +4,7 @@
 //   (trainers/promptsrc.py:144-168, :60; coop.py:259-296 "end"; cocoop.py:173-198),
 //   deep-prompt replacement and its gradient (model.py:232-252).
 #include <cooperative_groups.h>
+#include <type_traits>
 #include "common.cuh"
 
 namespace psrc {
@@ -25,7 +26,9 @@ __global__ void im2col_kernel(const float* __restrict__ img, T* __restrict__ out
     const int c = col / PP, rem = col - c * PP, ky = rem / P, kx = rem - ky * P;
     const float2 v = *reinterpret_cast<const float2*>(
         img + (((long long)(b * 3 + c) * R + gy * P + ky) * R + gx * P + kx));
-    if constexpr (sizeof(T) == 2) {
+    if constexpr (std::is_same<T, __half>::value) {
+      *reinterpret_cast<__half2*>(out + el) = __floats2half2_rn(v.x, v.y);
+    } else if constexpr (sizeof(T) == 2) {
       *reinterpret_cast<__nv_bfloat162*>(out + el) = __floats2bfloat162_rn(v.x, v.y);
     } else {
       *reinterpret_cast<float2*>(out + el) = v;
@@ -34,7 +37,8 @@ __global__ void im2col_kernel(const float* __restrict__ img, T* __restrict__ out
 }
 
 // P % 8 == 0 (ViT-B/16, ViT-B/32), 16-bit output: eight elements per thread -- two 16-byte loads, one 16-byte store
-__global__ void im2col8_kernel(const float* __restrict__ img, __nv_bfloat16* __restrict__ out, int B, int R, int P,
+template <typename T>
+__global__ void im2col8_kernel(const float* __restrict__ img, T* __restrict__ out, int B, int R, int P,
                                long long total8) {
   const int G = R / P, PP = P * P, K = 3 * PP;
   long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -49,11 +53,19 @@ __global__ void im2col8_kernel(const float* __restrict__ img, __nv_bfloat16* __r
         img + (((long long)(b * 3 + c) * R + gy * P + ky) * R + gx * P + kx));
     const float4 v0 = __ldg(src), v1 = __ldg(src + 1);
     uint4 u;
-    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
-    h[0] = __floats2bfloat162_rn(v0.x, v0.y);
-    h[1] = __floats2bfloat162_rn(v0.z, v0.w);
-    h[2] = __floats2bfloat162_rn(v1.x, v1.y);
-    h[3] = __floats2bfloat162_rn(v1.z, v1.w);
+    if constexpr (std::is_same<T, __half>::value) {
+      __half2* h = reinterpret_cast<__half2*>(&u);
+      h[0] = __floats2half2_rn(v0.x, v0.y);
+      h[1] = __floats2half2_rn(v0.z, v0.w);
+      h[2] = __floats2half2_rn(v1.x, v1.y);
+      h[3] = __floats2half2_rn(v1.z, v1.w);
+    } else {
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+      h[0] = __floats2bfloat162_rn(v0.x, v0.y);
+      h[1] = __floats2bfloat162_rn(v0.z, v0.w);
+      h[2] = __floats2bfloat162_rn(v1.x, v1.y);
+      h[3] = __floats2bfloat162_rn(v1.z, v1.w);
+    }
     *reinterpret_cast<uint4*>(out + el) = u;
   }
 }
@@ -81,7 +93,12 @@ assemble_vision_kernel(const T* __restrict__ pe, const float* __restrict__ cls, 
       } else if (l <= n_patches) {
         const T* src = pe + ((long long)b * n_patches + (l - 1)) * D + c;
         float4 a;
-        if constexpr (sizeof(T) == 2) {
+        if constexpr (std::is_same<T, __half>::value) {
+          uint2 u = *reinterpret_cast<const uint2*>(src);
+          float2 lo = __half22float2(*reinterpret_cast<__half2*>(&u.x));
+          float2 hi = __half22float2(*reinterpret_cast<__half2*>(&u.y));
+          a = make_float4(lo.x, lo.y, hi.x, hi.y);
+        } else if constexpr (sizeof(T) == 2) {
           uint2 u = *reinterpret_cast<const uint2*>(src);
           float2 lo = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.x));
           float2 hi = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.y));
@@ -267,8 +284,14 @@ extern "C" int psrc_im2col_patches(const float* image, void* patches, int out_dt
   const int G = R / P;
   const long long total2 = (long long)B * G * G * 3 * P * P / 2;
   const bool al16 = ((reinterpret_cast<uintptr_t>(image) | reinterpret_cast<uintptr_t>(patches)) & 15) == 0;
-  if (out_dtype == PSRC_BF16 && P % 8 == 0 && R % 4 == 0 && al16)
-    im2col8_kernel<<<grid_for(total2 / 4, 256), 256, 0, as_stream(stream)>>>(
+  if (out_dtype == PSRC_F16 && P % 8 == 0 && R % 4 == 0 && al16)
+    im2col8_kernel<__half><<<grid_for(total2 / 4, 256), 256, 0, as_stream(stream)>>>(
+        image, reinterpret_cast<__half*>(patches), B, R, P, total2 / 4);
+  else if (out_dtype == PSRC_F16)
+    im2col_kernel<__half><<<grid_for(total2, 256), 256, 0, as_stream(stream)>>>(
+        image, reinterpret_cast<__half*>(patches), B, R, P, total2);
+  else if (out_dtype == PSRC_BF16 && P % 8 == 0 && R % 4 == 0 && al16)
+    im2col8_kernel<__nv_bfloat16><<<grid_for(total2 / 4, 256), 256, 0, as_stream(stream)>>>(
         image, reinterpret_cast<__nv_bfloat16*>(patches), B, R, P, total2 / 4);
   else if (out_dtype == PSRC_BF16)
     im2col_kernel<__nv_bfloat16><<<grid_for(total2, 256), 256, 0, as_stream(stream)>>>(
@@ -311,6 +334,9 @@ extern "C" int psrc_assemble_vision_tokens(const void* patch_embed, int pe_dtype
   PSRC_CHECK_ARG(D > 0 && D % 4 == 0 && D <= 1024 && n_patches > 0 && n_ctx >= 0 && B >= 0,
                  "psrc_assemble_vision_tokens: bad shape");
   if (B == 0) return PSRC_OK;
+  if (pe_dtype == PSRC_F16)
+    return launch_assemble_vision<__half>(patch_embed, cls, pos, vpt, ln_g, ln_b, x, B, n_patches, n_ctx, D, eps,
+                                          as_stream(stream));
   if (pe_dtype == PSRC_BF16)
     return launch_assemble_vision<__nv_bfloat16>(patch_embed, cls, pos, vpt, ln_g, ln_b, x, B, n_patches, n_ctx, D,
                                                  eps, as_stream(stream));

@@ -5,12 +5,15 @@ launches; every FLOP runs in ``csrc/``.  Buffers are allocated once per (shape, 
 whole step can be captured into a CUDA graph.
 
 Data layout in HBM: activations are batch-first ``[n_seq * L, D]``; the residual
-stream is fp32; "act" tensors are bf16 (fast mode) or fp32 (validation mode); frozen weights
-are kept as ``W [out, in]`` (forward GEMM operand, K-major) plus ``W^T [in, out]`` (dgrad GEMM
-operand) in act dtype -- they are never given a weight-gradient pass
+stream is fp32; the 16-bit tensors of the fast mode follow ``TowerDtypes`` (fp16 forward operands,
+bf16 gradients; everything fp32 in the validation mode); frozen weights are kept as ``W [out, in]``
+(forward GEMM operand, K-major) plus ``W^T [in, out]`` (dgrad GEMM operand, gradient format) --
+they are never given a weight-gradient pass
 (PromptSRC/trainers/promptsrc.py:238-247).
 """
 from __future__ import annotations
+
+from typing import NamedTuple
 
 import torch
 
@@ -20,6 +23,30 @@ from .ops import ACT_QUICKGELU, ACT_QUICKGELU_GRAD
 ACT_DTYPES = {"bf16": torch.bfloat16, "fp32": torch.float32}
 
 
+class TowerDtypes(NamedTuple):
+    """Storage formats of one tower's 16-bit tensors in the fast mode (all fp32 in the validation mode).
+
+    fwd:  forward GEMM operands -- LN outputs, MLP hidden / pre-activation, W_qkv, W_fc1, W_fc2
+    attn: q/k/v, the attention output and W_o (the attention kernel's format)
+    grad: every gradient tensor and the transposed weights of the dgrad GEMMs
+
+    "fp16 forward" (DESIGN 2): forward operands in IEEE half -- CLIP's native inference format -- carry 3 more
+    mantissa bits than bf16 at the same tensor-core rate; gradients keep bf16's range.  The tcgen05 attention kernels
+    are bf16, so a tower whose sequences are longer than 32 tokens keeps bf16 q/k/v/O."""
+    fwd: torch.dtype
+    attn: torch.dtype
+    grad: torch.dtype
+
+
+def tower_dtypes(prec: str, L: int, fwd16: str = "fp16") -> TowerDtypes:
+    if prec == "fp32":
+        return TowerDtypes(torch.float32, torch.float32, torch.float32)
+    assert prec == "bf16" and fwd16 in ("fp16", "bf16"), (prec, fwd16)
+    if fwd16 == "bf16":
+        return TowerDtypes(torch.bfloat16, torch.bfloat16, torch.bfloat16)
+    return TowerDtypes(torch.float16, torch.float16 if L <= 32 else torch.bfloat16, torch.bfloat16)
+
+
 def _dev(t, device, dtype=torch.float32):
     return t.detach().to(device=device, dtype=dtype).contiguous()
 
@@ -27,24 +54,27 @@ def _dev(t, device, dtype=torch.float32):
 class BlockWeights:
     """One ResidualAttentionBlock (clip/model.py:167-188) in kernel layout."""
 
-    def __init__(self, sd, p, device, act, need_backward):
+    def __init__(self, sd, p, device, dt: TowerDtypes, need_backward):
         f = lambda k: _dev(sd[p + k], device)            # noqa: E731  fp32 vectors
-        a = lambda k: _dev(sd[p + k], device, act)       # noqa: E731  GEMM operands
+        a = lambda k: _dev(sd[p + k], device, dt.fwd)    # noqa: E731  forward GEMM operands
         self.ln1_g, self.ln1_b = f("ln_1.weight"), f("ln_1.bias")
         self.ln2_g, self.ln2_b = f("ln_2.weight"), f("ln_2.bias")
         self.wqkv, self.bqkv = a("attn.in_proj_weight"), f("attn.in_proj_bias")
-        self.wo, self.bo = a("attn.out_proj.weight"), f("attn.out_proj.bias")
+        self.wo, self.bo = _dev(sd[p + "attn.out_proj.weight"], device, dt.attn), f("attn.out_proj.bias")
         self.w1, self.b1 = a("mlp.c_fc.weight"), f("mlp.c_fc.bias")
         self.w2, self.b2 = a("mlp.c_proj.weight"), f("mlp.c_proj.bias")
         if need_backward:
-            t = lambda k: _dev(sd[p + k].t(), device, act)  # noqa: E731
+            t = lambda k: _dev(sd[p + k].t(), device, dt.grad)  # noqa: E731
             self.wqkv_t, self.wo_t = t("attn.in_proj_weight"), t("attn.out_proj.weight")
             self.w1_t, self.w2_t = t("mlp.c_fc.weight"), t("mlp.c_proj.weight")
 
 
 class TowerWeights:
-    def __init__(self, sd, prefix, n_layers, device, act, need_backward):
-        self.blocks = [BlockWeights(sd, f"{prefix}resblocks.{i}.", device, act, need_backward)
+    def __init__(self, sd, prefix, n_layers, device, dt, need_backward):
+        if not isinstance(dt, TowerDtypes):              # one dtype for everything (fp32 validation mode, tests)
+            dt = TowerDtypes(dt, dt, dt)
+        self.dt = dt
+        self.blocks = [BlockWeights(sd, f"{prefix}resblocks.{i}.", device, dt, need_backward)
                        for i in range(n_layers)]
         self.need_backward = need_backward
 
@@ -56,9 +86,10 @@ class Tower:
     overwritten with that layer's deep prompt before the block runs (clip/model.py:232-252).
     """
 
-    def __init__(self, weights: TowerWeights, n_seq, L, D, H, causal, act, save, device, prompt_layers=None):
+    def __init__(self, weights: TowerWeights, n_seq, L, D, H, causal, save, device, prompt_layers=None):
         self.w, self.n_seq, self.L, self.D, self.H, self.causal = weights, n_seq, L, D, H, causal
-        self.act, self.save, self.device = act, save, device
+        self.dt = dt = weights.dt            # storage formats follow the weights this tower multiplies with
+        self.act, self.save, self.device = dt.grad, save, device
         self.prompt_layers = dict(prompt_layers or {})
         # forward-only towers whose consumer reads only row 0 of every sequence (ln_post on the class token,
         # model.py:426): the last block's MLP then runs on n_seq rows instead of n_seq * L (set by the owner)
@@ -71,21 +102,21 @@ class Tower:
         # no residual byte crosses the SM); a tower that is differentiated keeps every layer's LayerNorm inputs
         self.X = [e(M, D) for _ in range(self.nl + 1 if save else 1)]
         self.X1 = [e(M, D) for _ in range(n_saved)] if save else [self.X[0]]
-        self.qkv = [e(M, 3 * D, dt=act) for _ in range(n_saved)]
-        self.O = [e(M, D, dt=act) for _ in range(n_saved)]
+        self.qkv = [e(M, 3 * D, dt=dt.attn) for _ in range(n_saved)]
+        self.O = [e(M, D, dt=dt.attn) for _ in range(n_saved)]
         self.lse = [e(n_seq, H, L) for _ in range(n_saved)]
-        self.u = [e(M, 4 * D, dt=act) for _ in range(n_saved)]
+        self.u = [e(M, 4 * D, dt=dt.fwd) for _ in range(n_saved)]
         self.stats = [[e(M) for _ in range(4)] for _ in range(n_saved)]  # mean1, rstd1, mean2, rstd2
-        self.h = e(M, D, dt=act)
-        self.g = e(M, 4 * D, dt=act)
-        self.hc = e(n_seq, D, dt=act)            # class-token rows of the last block (cls_only_last_mlp)
+        self.h = e(M, D, dt=dt.fwd)
+        self.g = e(M, 4 * D, dt=dt.fwd)
+        self.hc = e(n_seq, D, dt=dt.fwd)         # class-token rows of the last block (cls_only_last_mlp)
         if save:
             assert weights.need_backward
-            self.du = e(M, 4 * D, dt=act)
-            self.dh = e(M, D, dt=act)
-            self.dqkv = e(M, 3 * D, dt=act)
+            self.du = e(M, 4 * D, dt=dt.grad)
+            self.dh = e(M, D, dt=dt.grad)
+            self.dqkv = e(M, 3 * D, dt=dt.grad)
             self.dx = e(M, D)
-            self.dxa = e(M, D, dt=act) if act != torch.float32 else None
+            self.dxa = e(M, D, dt=dt.grad) if dt.grad != torch.float32 else None
 
     # -- buffers of layer i
     def _xin(self, i):

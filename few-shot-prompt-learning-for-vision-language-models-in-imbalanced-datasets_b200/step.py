@@ -14,15 +14,14 @@ so the summed result equals the single-device step.
 from __future__ import annotations
 
 import math
-from dataclasses import dataclass, field
-
 import os
+from dataclasses import dataclass, field
 
 import torch
 import torch.distributed as dist
 
 from . import ops
-from .engine import ACT_DTYPES, Tower, TowerWeights, _dev
+from .engine import ACT_DTYPES, Tower, TowerWeights, _dev, tower_dtypes
 from .synthetic import ClipArch
 
 
@@ -43,6 +42,9 @@ class StepConfig:
     w_logits: float = 1.0
     focal_alpha: list | None = None  # imbalance-aware CE (coop.py:326-346); None -> plain CE
     focal_gamma: float = 2.0
+    fwd16: str = field(default_factory=lambda: os.environ.get("PSRC_FWD16", "fp16"))
+    # ^ fast mode: 16-bit format of the FORWARD operands ("fp16": IEEE half, CLIP's native format, 3 more mantissa bits
+    #   than bf16 at the same tensor-core rate; "bf16").  Gradients are always bf16.  See engine.TowerDtypes.
     truncate_text: bool = True      # run text positions 0..max(EOT) only (exact)
     class_token_position: str = "end"   # CoOp: "end" | "middle" | "front" (coop.py:267-293)
     coupling: bool = False          # MaPLe: vision prompts = Linear_i(text prompts) (maple.py:145, :155-156, :199-204)
@@ -67,13 +69,14 @@ def encode_text_frozen(clip_sd: dict, tokens: torch.Tensor, device, prec: str = 
     tokens: int64 [N, 77].  Returns un-normalised features fp32 [N, E] on `device`."""
     from .synthetic import arch_from_state_dict
     a = arch_from_state_dict(clip_sd)
-    act = ACT_DTYPES[prec]
     dev = torch.device(device)
-    tw = TowerWeights(clip_sd, "transformer.", a.transformer_layers, dev, act, False)
+    tokens = tokens.to(torch.int64).cpu()
+    dts = tower_dtypes(prec, int(tokens.argmax(-1).max()) + 1)
+    act = dts.fwd
+    tw = TowerWeights(clip_sd, "transformer.", a.transformer_layers, dev, dts, False)
     tproj_t = _dev(clip_sd["text_projection"].t(), dev, act)
     ln_g, ln_b = _dev(clip_sd["ln_final.weight"], dev), _dev(clip_sd["ln_final.bias"], dev)
     pos = _dev(clip_sd["positional_embedding"], dev)
-    tokens = tokens.to(torch.int64).cpu()
     Dt, E = a.transformer_width, a.embed_dim
     out = torch.empty(tokens.shape[0], E, device=dev)
     for lo in range(0, tokens.shape[0], chunk):
@@ -82,7 +85,7 @@ def encode_text_frozen(clip_sd: dict, tokens: torch.Tensor, device, prec: str = 
         eot = tk.argmax(-1)
         L = int(eot.max()) + 1
         emb = _dev(clip_sd["token_embedding.weight"][tk], dev)               # model.py:606
-        tower = Tower(tw, n, L, Dt, a.transformer_heads, True, act, False, dev)
+        tower = Tower(tw, n, L, Dt, a.transformer_heads, True, False, dev)
         prefix, suffix = emb[:, :1].contiguous(), emb[:, 1:].contiguous()
         ops.assemble_text_prompts(prefix, suffix, prefix, pos, tower.x0, n, L, 0, Dt)   # + positional (model.py:608)
         tower.forward()
@@ -97,9 +100,18 @@ class PromptedClipStep:
         """clip_sd: reference-keyed CLIP state-dict (fp32).  tokens: int64 [C, 77] tokenised prompts."""
         self.cfg, self.device = cfg, torch.device(device)
         a = cfg.arch
-        self.act = ACT_DTYPES[cfg.prec]
         dev = self.device
         C, B = cfg.n_cls, cfg.batch
+        # ---- sequence lengths first: they decide the storage formats of each tower (engine.TowerDtypes)
+        tokens = tokens.to(torch.int64).cpu()
+        assert tokens.shape[0] == C
+        eot_all = tokens.argmax(-1)                                          # promptsrc.py:68
+        self.Lt = int(eot_all.max()) + 1 if cfg.truncate_text else a.context_length
+        self.Lv = 1 + a.n_patches + cfg.n_ctx_vision
+        self.vdt = tower_dtypes(cfg.prec, self.Lv, cfg.fwd16)
+        self.tdt = tower_dtypes(cfg.prec, self.Lt, cfg.fwd16)
+        self.act = self.vdt.grad          # gradient operands (and the fp32 validation mode's only format)
+        self.fwd = self.vdt.fwd           # forward operands outside the towers (patches, class-token / EOT rows)
         self.per_image = bool(cfg.per_image_text)
         if self.per_image:                        # CoCoOp: pure batch sharding, every rank runs all classes (SURVEY 8e)
             assert cfg.n_ctx_vision == 0 and cfg.depth_text == 1 and not cfg.zero_shot_branch and not cfg.ctx_per_class
@@ -127,25 +139,21 @@ class PromptedClipStep:
 
         # ---- frozen weights in kernel layout
         need_vb = cfg.n_ctx_vision > 0
-        self.vw = TowerWeights(clip_sd, "visual.transformer.", a.vision_layers, dev, self.act, need_vb)
-        self.tw = TowerWeights(clip_sd, "transformer.", a.transformer_layers, dev, self.act, True)
+        self.vw = TowerWeights(clip_sd, "visual.transformer.", a.vision_layers, dev, self.vdt, need_vb)
+        self.tw = TowerWeights(clip_sd, "transformer.", a.transformer_layers, dev, self.tdt, True)
         f = lambda k: _dev(clip_sd[k], dev)  # noqa: E731
-        self.conv_w = _dev(clip_sd["visual.conv1.weight"].reshape(self.Dv, -1), dev, self.act)
+        self.conv_w = _dev(clip_sd["visual.conv1.weight"].reshape(self.Dv, -1), dev, self.fwd)
         self.cls, self.vpos = f("visual.class_embedding"), f("visual.positional_embedding")
         self.ln_pre = (f("visual.ln_pre.weight"), f("visual.ln_pre.bias"))
         self.ln_post = (f("visual.ln_post.weight"), f("visual.ln_post.bias"))
         self.ln_final = (f("ln_final.weight"), f("ln_final.bias"))
         self.vproj = _dev(clip_sd["visual.proj"], dev, self.act)            # [Dv, E]  (dgrad operand)
-        self.vproj_t = _dev(clip_sd["visual.proj"].t(), dev, self.act)      # [E, Dv]  (forward operand)
+        self.vproj_t = _dev(clip_sd["visual.proj"].t(), dev, self.fwd)      # [E, Dv]  (forward operand)
         self.tproj = _dev(clip_sd["text_projection"], dev, self.act)        # [Dt, E]
-        self.tproj_t = _dev(clip_sd["text_projection"].t(), dev, self.act)  # [E, Dt]
+        self.tproj_t = _dev(clip_sd["text_projection"].t(), dev, self.fwd)  # [E, Dt]  (forward operand)
         self.tpos = f("positional_embedding")
 
         # ---- class tokens (this rank's shard): prefix / suffix embeddings, EOT rows
-        tokens = tokens.to(torch.int64).cpu()
-        assert tokens.shape[0] == C
-        eot_all = tokens.argmax(-1)                                          # promptsrc.py:68
-        self.Lt = int(eot_all.max()) + 1 if cfg.truncate_text else a.context_length
         emb = clip_sd["token_embedding.weight"][tokens[cls_idx]]             # promptsrc.py:121
         self.token_prefix = _dev(emb[:, :1], dev)                           # promptsrc.py:136
         self.token_suffix = _dev(emb[:, 1 + cfg.n_ctx_text:], dev)          # promptsrc.py:137
@@ -173,13 +181,12 @@ class PromptedClipStep:
 
         # ---- towers
         P = a.n_patches
-        self.Lv = 1 + P + cfg.n_ctx_vision
         v_prompts = {i: (1 + P, cfg.n_ctx_vision) for i in range(1, cfg.depth_vision)} if need_vb else {}
         t_prompts = {i: (1, cfg.n_ctx_text) for i in range(1, cfg.depth_text)}
-        self.vt = Tower(self.vw, B, self.Lv, self.Dv, a.vision_heads, False, self.act, need_vb, dev, v_prompts)
-        self.tt = Tower(self.tw, self.n_text_seq, self.Lt, self.Dt, a.transformer_heads, True, self.act, True, dev,
+        self.vt = Tower(self.vw, B, self.Lv, self.Dv, a.vision_heads, False, need_vb, dev, v_prompts)
+        self.tt = Tower(self.tw, self.n_text_seq, self.Lt, self.Dt, a.transformer_heads, True, True, dev,
                         t_prompts)
-        self.zt = Tower(self.vw, B, 1 + P, self.Dv, a.vision_heads, False, self.act, False, dev) \
+        self.zt = Tower(self.vw, B, 1 + P, self.Dv, a.vision_heads, False, False, dev) \
             if cfg.zero_shot_branch else None
         if self.zt is not None:
             self.zt.cls_only_last_mlp = True    # only ln_post(x[:, 0]) of the frozen tower is ever read (:301)
@@ -187,10 +194,10 @@ class PromptedClipStep:
             self.vt.cls_only_last_mlp = True    # CoOp / CoCoOp: forward-only image tower, only the class token is read
 
         e = lambda *s, dt=torch.float32: torch.empty(*s, device=dev, dtype=dt)  # noqa: E731
-        self.patches = e(B * P, 3 * a.vision_patch_size ** 2, dt=self.act)
-        self.pe = e(B * P, self.Dv, dt=self.act)
+        self.patches = e(B * P, 3 * a.vision_patch_size ** 2, dt=self.fwd)
+        self.pe = e(B * P, self.Dv, dt=self.fwd)
         Ts = self.n_text_seq
-        self.hv, self.ht = e(B, self.Dv, dt=self.act), e(Ts, self.Dt, dt=self.act)
+        self.hv, self.ht = e(B, self.Dv, dt=self.fwd), e(Ts, self.Dt, dt=self.fwd)
         self.hv_stats, self.ht_stats = (e(B), e(B)), (e(Ts), e(Ts))
         self.f, self.f_hat, self.f_inv = e(B, self.E), e(B, self.E), e(B)
         self.t, self.t_hat_l, self.t_inv = e(Ts, self.E), e(Ts, self.E), e(Ts)
@@ -217,13 +224,13 @@ class PromptedClipStep:
             if cfg.focal_alpha is not None else None
         if need_vb:
             self.vpt_rounded = e(cfg.n_ctx_vision, self.Dv)
-            self.vpt_scratch = e(cfg.n_ctx_vision, self.Dv, dt=self.act)
+            self.vpt_scratch = e(cfg.n_ctx_vision, self.Dv, dt=self.fwd)
             self.vpt_stats = (e(cfg.n_ctx_vision), e(cfg.n_ctx_vision))
             self.vpt_gsum = e(cfg.n_ctx_vision, self.Dv)
 
         # ---- frozen teacher (PromptSRC): ZS image features per step, fixed text embeddings once
         if cfg.zero_shot_branch:
-            self.zhv, self.zf = e(B, self.Dv, dt=self.act), e(B, self.E)
+            self.zhv, self.zf = e(B, self.Dv, dt=self.fwd), e(B, self.E)
             self.zf_hat, self.zs_logits = e(B, self.E), e(B, C)
             assert fixed_embeddings is not None, "PromptSRC needs the frozen-CLIP text embeddings"
             fe = _dev(fixed_embeddings, dev)                                   # [C, E] un-normalised
@@ -795,10 +802,10 @@ class VisionInference:
 
     def __init__(self, step: PromptedClipStep, batch: int):
         self.step, self.batch = step, batch
-        cfg, a, dev, act = step.cfg, step.cfg.arch, step.device, step.act
+        cfg, a, dev, act = step.cfg, step.cfg.arch, step.device, step.fwd
         P = a.n_patches
         v_prompts = {i: (1 + P, cfg.n_ctx_vision) for i in range(1, cfg.depth_vision)} if cfg.n_ctx_vision > 0 else {}
-        self.vt = Tower(step.vw, batch, step.Lv, step.Dv, a.vision_heads, False, act, False, dev, v_prompts)
+        self.vt = Tower(step.vw, batch, step.Lv, step.Dv, a.vision_heads, False, False, dev, v_prompts)
         self.vt.cls_only_last_mlp = True        # evaluation reads ln_post(x[:, 0]) only
         e = lambda *s, dt=torch.float32: torch.empty(*s, device=dev, dtype=dt)  # noqa: E731
         self.image = e(batch, 3, a.image_resolution, a.image_resolution)

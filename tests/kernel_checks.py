@@ -453,7 +453,99 @@ def check_small_layers(res: Results):
     res.add("assemble_text_prompts grouped (+bias)", max_err(x.view(B, C2, L, D), ref), 1e-6)
 
 
+# ----------------------------------------------------------------------------- fp16 forward operands
+def check_fp16_forward(res: Results):
+    """The "fp16 forward" storage formats (engine.TowerDtypes): fp16 A / W / 16-bit outputs of the tcgen05 GEMMs (and a
+    bf16 output from fp16 operands, the vision towers' q/k/v), fp16 aux of the QuickGELU' epilogue next to bf16
+    operands, fp16 LayerNorm / im2col outputs, and the short-sequence attention kernels with fp16 q/k/v/O forward and
+    fp16 q/k/v + bf16 dO -> bf16 dqkv backward.  Tolerances are the fp16 ones (3 more mantissa bits than bf16)."""
+    from psrc_b200 import ops
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(11)
+    h, b16 = torch.float16, torch.bfloat16
+    for backend_name, backend in (("pair", ops.GEMM_TCGEN05), ("1cta", ops.GEMM_TCGEN05_1CTA), ("simt", ops.GEMM_SIMT)):
+        shapes = [(300, 384, 768), (11000, 512, 512), (2048, 768, 3072)] if backend_name != "simt" else [(300, 384, 72)]
+        for (M, N, K) in shapes:
+            a = (torch.randn(M, K, device=dev, generator=g) * 0.5).to(h)
+            w = (torch.randn(N, K, device=dev, generator=g) * 0.5).to(h)
+            bias = torch.randn(N, device=dev, generator=g)
+            resid = torch.randn(M, N, device=dev, generator=g)
+            ref0 = a.float() @ w.float().t()
+            tag = f"gemm[{backend_name},fp16] {M}x{N}x{K}"
+            out = torch.full((M, N), float("nan"), device=dev)
+            ops.gemm(a, w, out, backend=backend)
+            res.add(tag + " plain/f32", rel_err(out, ref0), 1e-5)          # exact products, fp32 accumulation
+            for odt, tol in ((h, 6e-4), (b16, 6e-3)):
+                o16 = torch.empty(M, N, device=dev, dtype=odt)
+                ops.gemm(a, w, o16, bias=bias, backend=backend)
+                res.add(tag + f" bias/{str(odt)[6:]}", rel_err(o16, ref0 + bias), tol)
+            ro = torch.full((M, N), float("nan"), device=dev)
+            ops.gemm(a, w, ro, bias=bias, residual=resid, alpha=0.5, backend=backend)
+            res.add(tag + " bias+res", rel_err(ro, 0.5 * ref0 + bias + resid), 1e-5)
+            rs = resid.clone()
+            ops.gemm(a, w, rs, bias=bias, residual=rs, backend=backend)
+            res.add(tag + " bias+res inplace", rel_err(rs, ref0 + bias + resid), 1e-5)
+            og, pre = torch.empty(M, N, device=dev, dtype=h), torch.empty(M, N, device=dev, dtype=h)
+            ops.gemm(a, w, og, bias=bias, act=ops.ACT_QUICKGELU, out2=pre, backend=backend)
+            res.add(tag + " quickgelu", rel_err(og, quickgelu(ref0 + bias)), 2e-3)   # tanh.approx in the fast form
+            res.add(tag + " quickgelu pre-act", rel_err(pre, ref0 + bias), 6e-4)
+            # backward flavour: bf16 operands, fp16 saved pre-activation
+            ab, wb = a.to(b16), w.to(b16)
+            u = torch.randn(M, N, device=dev, generator=g).to(h)
+            od = torch.empty(M, N, device=dev, dtype=b16)
+            ops.gemm(ab, wb, od, act=ops.ACT_QUICKGELU_GRAD, aux=u, backend=backend)
+            res.add(tag + " quickgelu_grad (bf16 x bf16, fp16 aux)",
+                    rel_err(od, (ab.float() @ wb.float().t()) * quickgelu_grad(u.float())), 6e-3)
+    # LayerNorm / gathered LayerNorm / im2col / patch embeddings in fp16
+    rows, D = 1003, 768
+    x = torch.randn(rows, D, device=dev, generator=g) * 2 + 0.3
+    gam, bet = torch.randn(D, device=dev, generator=g), torch.randn(D, device=dev, generator=g)
+    y = torch.empty(rows, D, device=dev, dtype=h)
+    ops.layernorm_fwd(x, gam, bet, y, torch.empty(rows, device=dev), torch.empty(rows, device=dev))
+    res.add("layernorm_fwd fp16 out", rel_err(y, F.layer_norm(x, (D,), gam, bet, 1e-5)), 5e-4)
+    n_seq, L = 59, 17
+    yg = torch.empty(n_seq, D, device=dev, dtype=h)
+    ops.gather_ln_fwd(x[:n_seq * L], None, gam, bet, yg, None, None, n_seq, L, D)
+    res.add("gather_ln_fwd fp16 out", rel_err(yg, F.layer_norm(x[:n_seq * L][0::L], (D,), gam, bet, 1e-5)), 5e-4)
+    for (B, R, P) in ((3, 224, 16), (2, 224, 14)):
+        img = torch.randn(B, 3, R, R, device=dev, generator=g)
+        G = R // P
+        patches = torch.empty(B * G * G, 3 * P * P, device=dev, dtype=h)
+        ops.im2col_patches(img, patches, R, P)
+        ref = F.unfold(img, P, stride=P).transpose(1, 2).reshape(B * G * G, 3 * P * P)
+        res.add(f"im2col fp16 B={B} R={R} P={P}", max_err(patches, ref.to(h)), 0.0)
+    B, npatch, n_ctx = 3, 196, 4
+    pe = torch.randn(B * npatch, D, device=dev, generator=g).to(h)
+    cls, pos = torch.randn(D, device=dev, generator=g), torch.randn(npatch + 1, D, device=dev, generator=g)
+    vpt = torch.randn(n_ctx, D, device=dev, generator=g) * 0.02
+    xo = torch.full((B * (1 + npatch + n_ctx), D), float("nan"), device=dev)
+    ops.assemble_vision_tokens(pe, cls, pos, vpt, gam, bet, xo, B, npatch, n_ctx, D)
+    xr = torch.cat([cls.expand(B, 1, D), pe.float().view(B, npatch, D)], 1) + pos
+    xr = torch.cat([xr, vpt.half().float().expand(B, n_ctx, D)], 1)
+    res.add("assemble_vision_tokens pe=fp16", rel_err(xo, F.layer_norm(xr, (D,), gam, bet, 1e-5).reshape(-1, D)), 1e-5)
+    # short-sequence attention: fp16 forward operands, bf16 gradients
+    for (n_seq, L, H, causal) in [(7, 16, 8, True), (4, 9, 2, True), (1001, 11, 8, True), (2, 1, 2, True),
+                                  (3, 16, 3, False), (3, 32, 8, True), (3, 17, 2, False), (130, 24, 8, True),
+                                  (4, 20, 12, True)]:
+        Dm = H * 64
+        qkv = torch.randn(n_seq * L, 3 * Dm, device=dev, generator=g).to(h)
+        qr = qkv.float().clone().requires_grad_(True)
+        o_ref, lse_ref = _attn_ref(qr, n_seq, L, H, causal)
+        out = torch.full((n_seq * L, Dm), float("nan"), device=dev, dtype=h)
+        lse = torch.full((n_seq, H, L), float("nan"), device=dev)
+        ops.attn_fwd(qkv, out, lse, n_seq, L, H, causal)
+        tag = f"attn[small_mma,fp16] n={n_seq} L={L} H={H} causal={int(causal)}"
+        res.add(tag + " out", rel_err(out, o_ref), 1e-3)
+        res.add(tag + " lse", max_err(lse, lse_ref), 2e-3)
+        dout = torch.randn(n_seq * L, Dm, device=dev, generator=g).to(b16)
+        o_ref.backward(dout.float())
+        dqkv = torch.full((n_seq * L, 3 * Dm), float("nan"), device=dev, dtype=b16)
+        ops.attn_bwd(qkv, out, dout, lse, dqkv, n_seq, L, H, causal)
+        res.add(tag + " dqkv (bf16)", rel_err(dqkv, qr.grad), 2e-2)
+
+
 GROUPS = {
+    "fp16_forward": check_fp16_forward,
     "small_layers": check_small_layers,
     "gemm_simt": lambda r: check_gemm(r, "simt"),
     "gemm_tc": lambda r: check_gemm(r, "tc"),
