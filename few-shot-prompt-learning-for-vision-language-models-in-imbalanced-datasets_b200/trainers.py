@@ -383,7 +383,7 @@ class _CustomCLIPBase(nn.Module):
         self._step = PromptedClipStep(scfg, sd, tokens, dev, fixed_embeddings=fixed_embeddings)
         self._infer = None
         self._test_batch = int(_get(cfg, "DATALOADER.TEST.BATCH_SIZE", 100))
-        self._use_graph = bool(_get(cfg, "TRAINER.B200.CUDA_GRAPH", True)) and world == 1
+        self._use_graph = bool(_get(cfg, "TRAINER.B200.CUDA_GRAPH", True)) and world == 1 and dev.type == "cuda"
         self._eager_steps = 0
         emb = sd["token_embedding.weight"][tokens]
         n_ctx = scfg.n_ctx_text
@@ -407,6 +407,13 @@ class _CustomCLIPBase(nn.Module):
                 p.grad = st.grads[k]
                 p.requires_grad_(True)
         self._named_prompts = named
+        # everything else is frozen, as the reference trainers' build_model leaves it (promptsrc.py:238-247,
+        # coop.py:419-421): a CLIP module that arrives with requires_grad=True everywhere (load_clip_to_cpu) must not
+        # show up as trainable in named_parameters() / checkpoints' optimizer state
+        prompt_ids = {id(p) for _, p in named}
+        for p in self.parameters():
+            if id(p) not in prompt_ids:
+                p.requires_grad_(False)
         return st
 
     # -- reference behaviour: everything except the prompts is frozen (promptsrc.py:238-247, coop.py:419-421)
@@ -433,6 +440,14 @@ class _CustomCLIPBase(nn.Module):
             return self._step.per_image_logits_for(image.float())
         if self._infer is None:
             self._infer = VisionInference(self._step, self._test_batch)
+        # The cached text features follow the prompts.  Dassl reaches CoOp's / CoCoOp's prompts through the REGISTERED
+        # sub-module only (`prompt_learner.eval()`, `prompt_learner.load_state_dict()` in load_model -- e.g. the
+        # best-val checkpoint before the final test), which never passes through this module's train() /
+        # load_state_dict() overrides; every such torch-level write bumps the tensors' version counters.
+        ver = sum(p._version for _, p in self._named_prompts)
+        if ver != getattr(self, "_eval_param_version", None):
+            self._infer.text_valid = False
+            self._eval_param_version = ver
         return self._infer.logits_for(image.float())
 
     def make_optimizer(self, optim_cfg):
@@ -460,7 +475,7 @@ class _CustomCLIPBase(nn.Module):
         if ver != getattr(self, "_param_version", None):
             st.invalidate_text()
             self._param_version = ver
-        if image.is_cuda:
+        if image.is_cuda or st.device.type != "cuda":     # (CPU: host-logic tests over restated kernels only)
             st.image.copy_(image, non_blocking=True)
             st.labels.copy_(label.to(torch.int32), non_blocking=True)
             st.run()
@@ -468,7 +483,8 @@ class _CustomCLIPBase(nn.Module):
             st.run_staged()                  # this batch was copied over while the previous step was running
         else:
             st.run_host(image, label)        # H2D on the copy stream, under the text-tower forward
-        if next_batch is not None and not next_batch[0].is_cuda and next_batch[0].shape[0] == st.cfg.batch:
+        if next_batch is not None and not next_batch[0].is_cuda and next_batch[0].shape[0] == st.cfg.batch \
+                and st.device.type == "cuda":
             st.stage_host(*next_batch)       # the following batch starts its H2D under this step's compute
         if self._infer is not None:
             self._infer.text_valid = False
@@ -479,10 +495,17 @@ class _CustomCLIPBase(nn.Module):
         host does not wait for the next step's text-tower prefix that is already enqueued behind it."""
         return self._step.loss_value()
 
+    def params_changed(self):
+        """Call after writing the prompt buffer from outside the fused step (checkpoint load, GPA, a foreign
+        optimizer): drops the text prefix enqueued ahead and the evaluation path's cached text features."""
+        if getattr(self, "_step", None) is not None:
+            self._step.invalidate_text()
+        if getattr(self, "_infer", None) is not None:
+            self._infer.text_valid = False
+
     def load_state_dict(self, *args, **kwargs):
         out = super().load_state_dict(*args, **kwargs)
-        if getattr(self, "_step", None) is not None:
-            self._step.invalidate_text()      # prompt parameters changed behind the step's back
+        self.params_changed()                 # prompt parameters changed behind the step's back
         return out
 
 
@@ -863,7 +886,7 @@ class PromptSRC(_PromptTrainer):
             if self.step_counter == self.model.total_epochs + 1:
                 print("Using GPA model for final inference...")
                 self.model._step.flat_param.copy_(self.previous_model_gpa)
-                self.model._step.invalidate_text()       # a text prefix enqueued ahead used the pre-GPA prompts
+                self.model.params_changed()              # text prefix enqueued ahead / cached eval text: pre-GPA prompts
         elif last:
             self.update_lr()
         return loss_summary

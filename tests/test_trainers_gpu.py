@@ -36,6 +36,20 @@ def test_eval_logits_cached_text_and_checkpoint_roundtrip():
     assert m["eval_logits_maxabs"] < 1e-4 and m["eval_argmax_equal"] and m["eval_shape_ok"], m
 
 
+def test_promptsrc_gpa_three_epochs_matches_reference_aggregation():
+    _need_gpu()
+    m = TC.check_gpa("fp32")
+    assert m["step_counter"] == 4 and m["loss_abs_max"] < 5e-5, m
+    assert m["gpa_param_maxabs"] < 1e-6 and m["last_vs_gpa_maxabs"] > 1e-5, m    # GPA != the last iterate
+    assert m["eval_logits_maxabs"] < 1e-4, m
+
+
+def test_coop_eval_text_cache_follows_prompt_learner_load_state_dict():
+    _need_gpu()
+    m = TC.check_coop_eval_follows_prompt_learner_load()
+    assert m["changed_maxabs"] > 1e-3 and m["stale_maxabs"] == 0.0, m
+
+
 @pytest.mark.parametrize("loss_type", ["ce", "focal"])
 def test_coop_trainer_step(loss_type):
     _need_gpu()

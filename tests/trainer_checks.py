@@ -178,6 +178,74 @@ def check_eval_and_checkpoint(prec="fp32"):
     return m
 
 
+
+def check_gpa(prec="fp32"):
+    """USE_GPA = True over 3 epochs x 2 batches (promptsrc.py:335-360): after every epoch the prompts enter the running
+    Gaussian-weighted sum (`state_dict_weighting` / `state_dict_add`, :363-378), after the last one the sum replaces
+    the model.  Restated here on the oracle's parameters after the same SGD steps with the trainer's own lr schedule;
+    the frozen tensors are scaled by weights that sum to 1, i.e. unchanged, so only the prompts are compared."""
+    import numpy as np
+    from psrc_b200 import synthetic as S
+    epochs, nb = 3, 2
+    tr, cfg, tokens = make_trainer("PromptSRC", prec, **{"TRAINER.PROMPTSRC.USE_GPA": True, "OPTIM.MAX_EPOCH": epochs})
+    tr.num_batches = nb
+    image, label = S.synthetic_batch(B, tokens.shape[0], 64, seed=1)
+    batch = {"img": image.pin_memory(), "label": label.pin_memory()}
+    lrs, losses = [], []
+    for e in range(epochs):
+        for b in range(nb):
+            tr.epoch, tr.batch_idx = e, b
+            lrs.append(tr.optim.param_groups[0]["lr"])
+            losses.append(tr.forward_backward(batch)["loss"])
+    ref, _, _ = oracle_promptsrc(tokens, image, label, steps=epochs * nb, lrs=tuple(lrs))
+    mean, std = cfg.TRAINER.PROMPTSRC.GPA_MEAN, cfg.TRAINER.PROMPTSRC.GPA_STD
+    g = np.array([1 / (std * np.sqrt(2 * np.pi)) * np.exp(-0.5 * ((a - mean) / std) ** 2) for a in range(1, epochs + 1)])
+    g = g / g.sum()
+    gpa = {k: sum(float(g[e]) * ref[(e + 1) * nb - 1]["params"][k] for e in range(epochs)) for k in ref[0]["params"]}
+    named = dict(tr.model.named_parameters())
+    m = {"loss_abs_max": max(abs(l - r["loss"]) for l, r in zip(losses, ref)),
+         "lrs": lrs,
+         "gpa_param_maxabs": max(float((named[k].detach().cpu() - v).abs().max()) for k, v in gpa.items()),
+         "last_vs_gpa_maxabs": max(float((ref[-1]["params"][k] - v).abs().max()) for k, v in gpa.items()),
+         "step_counter": tr.step_counter}
+    # the evaluation path must see the aggregated prompts (cached text features dropped by params_changed)
+    import clip_oracle as O
+    arch = S.ARCHS["tiny"]
+    sd = S.make_clip_state_dict(arch, seed=0)
+    tr.set_model_mode("eval")
+    img7, _ = S.synthetic_batch(7, tokens.shape[0], 64, seed=5)
+    with torch.no_grad():
+        lg = tr.model_inference(img7.cuda()).cpu()
+        dv = {i: gpa[f"image_encoder.transformer.resblocks.{i}.VPT_shallow"] for i in range(1, DEPTH)}
+        dt = {i: gpa[f"text_encoder.transformer.resblocks.{i}.VPT_shallow"] for i in range(1, DEPTH)}
+        emb = sd["token_embedding.weight"][tokens]
+        t = O.normalize(O.text_tower(O.construct_prompts(emb[:, :1], gpa["prompt_learner.ctx"], emb[:, 1 + N_CTX:]),
+                                     tokens.argmax(-1), sd, arch.transformer_heads, dt, N_CTX))
+        f = O.normalize(O.vision_tower(img7, sd, arch.vision_heads, gpa["image_encoder.VPT"], dv))
+        m["eval_logits_maxabs"] = float((lg - sd["logit_scale"].exp() * f @ t.t()).abs().max())
+    return m
+
+
+def check_coop_eval_follows_prompt_learner_load():
+    """Dassl reaches CoOp's prompts through the registered `prompt_learner` only.  eval -> load other
+    prompts through `prompt_learner.load_state_dict` (what `load_model` does before the final test) -> eval must score
+    the LOADED prompts, not the cached text features of the previous ones."""
+    from psrc_b200 import synthetic as S
+    tr, cfg, tokens = make_trainer("CoOp", "fp32")
+    img7, _ = S.synthetic_batch(7, tokens.shape[0], 64, seed=5)
+    tr.set_model_mode("eval")
+    with torch.no_grad():
+        lg0 = tr.model_inference(img7.cuda()).clone()
+        sd_pl = {k: v.clone() for k, v in tr.model.prompt_learner.state_dict().items()}
+        sd_pl["ctx"] = sd_pl["ctx"] + 0.05 * torch.randn_like(sd_pl["ctx"])
+        tr.model.prompt_learner.load_state_dict(sd_pl)
+        lg1 = tr.model_inference(img7.cuda()).clone()
+        # ground truth for the loaded prompts: a fresh text pass
+        tr.model._infer.text_valid = False
+        lg2 = tr.model_inference(img7.cuda()).clone()
+    return {"changed_maxabs": float((lg1 - lg0).abs().max()), "stale_maxabs": float((lg1 - lg2).abs().max())}
+
+
 def _seed_trainer_params(tr, values):
     """Overwrite the trainer's (randomly initialised) prompt-learner parameters with seeded values."""
     named = dict(tr.model.prompt_learner.named_parameters())
