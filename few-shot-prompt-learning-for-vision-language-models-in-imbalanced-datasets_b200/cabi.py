@@ -65,7 +65,7 @@ SIGNATURES = {
     "psrc_insert_prompt": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "psrc_prompt_grad": (_i, [_vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "psrc_gather_ln_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _f, _vp]),
-    "psrc_gather_ln_bwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "psrc_gather_ln_bwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "psrc_l2norm_fwd": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "psrc_l2norm_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp]),
     "psrc_loss_fwd_bwd": (_i, [C.POINTER(LossArgs), _vp]),

@@ -287,13 +287,13 @@ extern "C" int psrc_gather_ln_fwd(const float* x, const int32_t* idx, const floa
 }
 
 extern "C" int psrc_gather_ln_bwd(const void* dy, int dy_dtype, const float* x, const int32_t* idx,
-                                  const float* gamma, const float* mean, const float* rstd, float* dx,
-                                  void* dx_act, int act_dtype, int n_seq, int L, int D,
-                                  psrc_stream_t stream) {
+                                  const float* gamma, const float* mean, const float* rstd,
+                                  const float* dx_in, float* dx, void* dx_act, int act_dtype, int n_seq, int L,
+                                  int D, psrc_stream_t stream) {
   const int rows = n_seq * L;
   CHECK_LN_COMMON("psrc_gather_ln_bwd");
   PSRC_CHECK_ARG(dy && x && gamma && mean && rstd && dx && L > 0, "psrc_gather_ln_bwd: bad arguments");
   if (rows == 0) return PSRC_OK;
-  return bwd_dispatch(dy, dy_dtype, x, idx, L, gamma, mean, rstd, nullptr, dx, dx_act, act_dtype, rows, D,
+  return bwd_dispatch(dy, dy_dtype, x, idx, L, gamma, mean, rstd, dx_in, dx, dx_act, act_dtype, rows, D,
                       as_stream(stream));
 }

@@ -91,8 +91,9 @@ class Tower:
         self.dt = dt = weights.dt            # storage formats follow the weights this tower multiplies with
         self.act, self.save, self.device = dt.grad, save, device
         self.prompt_layers = dict(prompt_layers or {})
-        # forward-only towers whose consumer reads only row 0 of every sequence (ln_post on the class token,
-        # model.py:426): the last block's MLP then runs on n_seq rows instead of n_seq * L (set by the owner)
+        # towers whose consumer reads only row 0 of every sequence (ln_post on the class token, model.py:426) and whose
+        # gradient therefore enters on row 0 only: the last block's out-projection, LN2 and MLP -- and their
+        # input-gradients -- run on n_seq rows instead of n_seq * L (set by the owner)
         self.cls_only_last_mlp = False
         self.nl = len(weights.blocks)
         M = self.M = n_seq * L
@@ -114,6 +115,7 @@ class Tower:
             assert weights.need_backward
             self.du = e(M, 4 * D, dt=dt.grad)
             self.dh = e(M, D, dt=dt.grad)
+            self.dhc = e(n_seq, D, dt=dt.grad)       # class-token rows of the last block (cls_only_last_mlp)
             self.dqkv = e(M, 3 * D, dt=dt.grad)
             self.dx = e(M, D)
             self.dxa = e(M, D, dt=dt.grad) if dt.grad != torch.float32 else None
@@ -146,15 +148,20 @@ class Tower:
             ops.layernorm_fwd(x0, b.ln1_g, b.ln1_b, self.h, mean1, rstd1)
             ops.gemm(self.h, b.wqkv, self.qkv[s], bias=b.bqkv)
             ops.attn_fwd(self.qkv[s], self.O[s], self.lse[s], n_seq, L, H, self.causal)
-            ops.gemm(self.O[s], b.wo, x1, bias=b.bo, residual=x0)
-            if self.cls_only_last_mlp and not self.save and i == self.nl - 1:
-                # x1 is x2 here (in place); only the class-token rows go through LN2 and the MLP, as a strided view
-                xc = x1.view(n_seq, L, D)[:, 0]
+            if self.cls_only_last_mlp and i == self.nl - 1:
+                # Last block, consumer reads row 0 only: every token's K / V still feed the class-token query, so the
+                # block runs up to the attention core on all rows; the out-projection, LN2 and the MLP run on the
+                # n_seq class-token rows, addressed as strided views (row stride L * D) of the full-size buffers.
+                # Row-wise identical arithmetic: exact.  The other rows of x1 / x2 are never written nor read.
+                oc, x0c, x1c, x2c = (t.view(n_seq, L, D)[:, 0] for t in (self.O[s], x0, x1, x2))
                 gc = self.g[:n_seq]
-                ops.gather_ln_fwd(x1, None, b.ln2_g, b.ln2_b, self.hc, None, None, n_seq, L, D)
-                ops.gemm(self.hc, b.w1, gc, bias=b.b1, act=ACT_QUICKGELU)
-                ops.gemm(gc, b.w2, xc, bias=b.b2, residual=xc)
+                ops.gemm(oc, b.wo, x1c, bias=b.bo, residual=x0c)
+                ops.gather_ln_fwd(x1, None, b.ln2_g, b.ln2_b, self.hc, mean2[:n_seq] if self.save else None,
+                                  rstd2[:n_seq] if self.save else None, n_seq, L, D)
+                ops.gemm(self.hc, b.w1, gc, bias=b.b1, act=ACT_QUICKGELU, out2=self.u[s][:n_seq] if self.save else None)
+                ops.gemm(gc, b.w2, x2c, bias=b.b2, residual=x1c)
                 continue
+            ops.gemm(self.O[s], b.wo, x1, bias=b.bo, residual=x0)
             ops.layernorm_fwd(x1, b.ln2_g, b.ln2_b, self.h, mean2, rstd2)
             ops.gemm(self.h, b.w1, self.g, bias=b.b1, act=ACT_QUICKGELU, out2=self.u[s] if self.save else None)
             ops.gemm(self.g, b.w2, x2, bias=b.b2, residual=x1)
@@ -171,12 +178,25 @@ class Tower:
         for i in range(self.nl - 1, stop_at_layer - 1, -1):
             b = self.w.blocks[i]
             mean1, rstd1, mean2, rstd2 = self.stats[i]
-            # MLP branch: x2 = x1 + W2 . gelu(W1 . LN2(x1))
-            ops.gemm(dxa, b.w2_t, self.du, act=ACT_QUICKGELU_GRAD, aux=self.u[i])
-            ops.gemm(self.du, b.w1_t, self.dh)
-            ops.layernorm_bwd(self.dh, self.X1[i], b.ln2_g, mean2, rstd2, dx, dx_in=dx, dx_act=self.dxa)
-            # attention branch: x1 = x0 + Wo . attn(Wqkv . LN1(x0))
-            ops.gemm(dxa, b.wo_t, self.dh)
+            if self.cls_only_last_mlp and i == self.nl - 1:
+                # the incoming gradient is non-zero on the class-token rows only (it came through gather_ln_bwd with
+                # idx = None, which zeroes every other row of dx / dxa): the MLP branch and the out-projection are
+                # differentiated on those n_seq rows; d(attention output) of every other row is zero
+                dxac = dxa.view(n_seq, L, D)[:, 0]
+                duc = self.du[:n_seq]
+                ops.gemm(dxac, b.w2_t, duc, act=ACT_QUICKGELU_GRAD, aux=self.u[i][:n_seq])
+                ops.gemm(duc, b.w1_t, self.dhc)
+                ops.gather_ln_bwd(self.dhc, self.X1[i], None, b.ln2_g, mean2[:n_seq], rstd2[:n_seq], dx, n_seq, L, D,
+                                  dx_act=self.dxa, dx_in=dx)
+                self.dh.zero_()
+                ops.gemm(dxac, b.wo_t, self.dh.view(n_seq, L, D)[:, 0])
+            else:
+                # MLP branch: x2 = x1 + W2 . gelu(W1 . LN2(x1))
+                ops.gemm(dxa, b.w2_t, self.du, act=ACT_QUICKGELU_GRAD, aux=self.u[i])
+                ops.gemm(self.du, b.w1_t, self.dh)
+                ops.layernorm_bwd(self.dh, self.X1[i], b.ln2_g, mean2, rstd2, dx, dx_in=dx, dx_act=self.dxa)
+                # attention branch: x1 = x0 + Wo . attn(Wqkv . LN1(x0))
+                ops.gemm(dxa, b.wo_t, self.dh)
             ops.attn_bwd(self.qkv[i], self.O[i], self.dh, self.lse[i], self.dqkv, n_seq, L, H, self.causal)
             ops.gemm(self.dqkv, b.wqkv_t, self.dh)
             ops.layernorm_bwd(self.dh, self.X[i], b.ln1_g, mean1, rstd1, dx, dx_in=dx, dx_act=self.dxa)

@@ -131,9 +131,9 @@ def gather_ln_fwd(x, idx, gamma, beta, y, mean, rstd, n_seq, L, D, eps=LN_EPS):
     return y
 
 
-def gather_ln_bwd(dy, x, idx, gamma, mean, rstd, dx, n_seq, L, D, dx_act=None):
+def gather_ln_bwd(dy, x, idx, gamma, mean, rstd, dx, n_seq, L, D, dx_act=None, dx_in=None):
     cabi.check(cabi.load().psrc_gather_ln_bwd(ptr(dy), dt(dy), ptr(x), ptr(idx), ptr(gamma), ptr(mean), ptr(rstd),
-                                              ptr(dx), ptr(dx_act), dt(dx_act) if dx_act is not None else F32,
+                                              ptr(dx_in), ptr(dx), ptr(dx_act), dt(dx_act) if dx_act is not None else F32,
                                               n_seq, L, D, cabi.stream()), "psrc_gather_ln_bwd")
     return dx
 

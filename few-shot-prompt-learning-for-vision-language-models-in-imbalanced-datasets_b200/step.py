@@ -190,8 +190,8 @@ class PromptedClipStep:
             if cfg.zero_shot_branch else None
         if self.zt is not None:
             self.zt.cls_only_last_mlp = True    # only ln_post(x[:, 0]) of the frozen tower is ever read (:301)
-        if not need_vb:
-            self.vt.cls_only_last_mlp = True    # CoOp / CoCoOp: forward-only image tower, only the class token is read
+        # only ln_post(x[:, 0]) is read (model.py:426), with or without a backward (PSRC_CLS_ONLY=0: A/B switch)
+        self.vt.cls_only_last_mlp = need_vb is False or os.environ.get("PSRC_CLS_ONLY", "1") != "0"
 
         e = lambda *s, dt=torch.float32: torch.empty(*s, device=dev, dtype=dt)  # noqa: E731
         self.patches = e(B * P, 3 * a.vision_patch_size ** 2, dt=self.fwd)

@@ -173,11 +173,15 @@ int psrc_gather_ln_fwd(const float* x, const int32_t* idx, const float* gamma,
                        float* rstd, int n_seq, int L, int D, float eps,
                        psrc_stream_t stream);
 /* backward: dx (fp32 [n_seq*L, D]) is fully written: zeros everywhere except the
- * gathered rows, which receive LN'(dy); dx_act (optional) is the same in act dtype. */
+ * gathered rows, which receive LN'(dy) (+ dx_in at those rows when dx_in != NULL --
+ * the residual-branch gradient; dx_in may alias dx); dx_act (optional) is the same
+ * in act dtype.  With dx_in this is also the LN2 backward of a block whose MLP ran
+ * on the gathered rows only (the last block: only ln_post(x[:,0]) / the EOT row is
+ * ever read, model.py:426, promptsrc.py:64-68). */
 int psrc_gather_ln_bwd(const void* dy, int dy_dtype, const float* x, const int32_t* idx,
                        const float* gamma, const float* mean, const float* rstd,
-                       float* dx, void* dx_act, int act_dtype, int n_seq, int L, int D,
-                       psrc_stream_t stream);
+                       const float* dx_in, float* dx, void* dx_act, int act_dtype,
+                       int n_seq, int L, int D, psrc_stream_t stream);
 /* promptsrc.py:190-191 `f / f.norm(dim=-1, keepdim=True)`; inv_norm saved. */
 int psrc_l2norm_fwd(const float* x, float* y, float* inv_norm, int rows, int D,
                     psrc_stream_t stream);

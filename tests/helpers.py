@@ -271,7 +271,7 @@ class FakeKernels:
         assert idx is None or (idx.shape == (n_seq,) and idx.dtype == torch.int32 and int(idx.max()) < L)
         return y
 
-    def gather_ln_bwd(self, dy, x, idx, gamma, mean, rstd, dx, n_seq, L, D, dx_act=None):
+    def gather_ln_bwd(self, dy, x, idx, gamma, mean, rstd, dx, n_seq, L, D, dx_act=None, dx_in=None):
         self._rec("gather_ln_bwd")
         assert dy.shape == (n_seq, D) and x.shape == dx.shape == (n_seq * L, D) and mean.shape == (n_seq,)
         return dx

@@ -269,5 +269,9 @@ def test_maple_cocoop_sharded_step_world2_gloo(kind):
         assert float((o["logits"] - ref["logits"][r * Bl:(r + 1) * Bl]).abs().max()) < 1e-5
         assert float((o["losses"] - ref["losses"]).abs().max()) < 1e-5, (o["losses"], ref["losses"])
         assert cos(o["grad"], ref["grad"]) > 0.999999
-        assert float((o["grad"] - ref["grad"]).abs().max()) < 1e-4 * float(ref["grad"].abs().max())
+        # per-sequence prompt gradients pass through fp16 (autograd of `.half()`, model.py:238): a different fp32
+        # summation order (2 vs 4 images per GEMM) may flip single fp16 roundings -- the error is quantised in fp16 ulps
+        # of one sequence's gradient element (measured 8.0e-5 or 1.6e-4 of max|grad| = one or two flips; identical
+        # with exact fp64 accumulation in the restated GEMMs, with or without the last-block pruning): bound = 2^-10
+        assert float((o["grad"] - ref["grad"]).abs().max()) < 2.0 ** -10 * float(ref["grad"].abs().max())
     assert float((out[0]["param"] - out[1]["param"]).abs().max()) == 0.0

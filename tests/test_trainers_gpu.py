@@ -40,7 +40,7 @@ def test_promptsrc_gpa_three_epochs_matches_reference_aggregation():
     _need_gpu()
     m = TC.check_gpa("fp32")
     assert m["step_counter"] == 4 and m["loss_abs_max"] < 5e-5, m
-    assert m["gpa_param_maxabs"] < 1e-6 and m["last_vs_gpa_maxabs"] > 1e-5, m    # GPA != the last iterate
+    assert m["gpa_param_maxabs"] < 1e-5 and m["last_vs_gpa_maxabs"] > 1e-3, m    # GPA != the last iterate
     assert m["eval_logits_maxabs"] < 1e-4, m
 
 

@@ -188,10 +188,13 @@ class TorchKernels:
         return y
 
     @classmethod
-    def gather_ln_bwd(cls, dy, x, idx, gamma, mean, rstd, dx, n_seq, L, D, dx_act=None):
+    def gather_ln_bwd(cls, dy, x, idx, gamma, mean, rstd, dx, n_seq, L, D, dx_act=None, dx_in=None):
         r = cls._rows(idx, n_seq, L)
+        d = _ln_bwd(dy, x[r], gamma, mean, rstd)
+        if dx_in is not None:
+            d = d + dx_in[r]
         dx.zero_()
-        dx[r] = _ln_bwd(dy, x[r], gamma, mean, rstd)
+        dx[r] = d
         if dx_act is not None:
             dx_act.copy_(dx)
         return dx
