@@ -59,6 +59,8 @@ SIGNATURES = {
     "psrc_layernorm_bwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "psrc_attn_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "psrc_attn_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "psrc_attn_row_fwd": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp]),
+    "psrc_attn_row_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _i, _i, _vp]),
     "psrc_im2col_patches": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "psrc_assemble_vision_tokens": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _vp]),
     "psrc_assemble_text_prompts": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp]),

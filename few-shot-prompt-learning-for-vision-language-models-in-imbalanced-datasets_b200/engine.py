@@ -147,12 +147,13 @@ class Tower:
             mean1, rstd1, mean2, rstd2 = self.stats[s]
             ops.layernorm_fwd(x0, b.ln1_g, b.ln1_b, self.h, mean1, rstd1)
             ops.gemm(self.h, b.wqkv, self.qkv[s], bias=b.bqkv)
-            ops.attn_fwd(self.qkv[s], self.O[s], self.lse[s], n_seq, L, H, self.causal)
             if self.cls_only_last_mlp and i == self.nl - 1:
-                # Last block, consumer reads row 0 only: every token's K / V still feed the class-token query, so the
-                # block runs up to the attention core on all rows; the out-projection, LN2 and the MLP run on the
-                # n_seq class-token rows, addressed as strided views (row stride L * D) of the full-size buffers.
-                # Row-wise identical arithmetic: exact.  The other rows of x1 / x2 are never written nor read.
+                # Last block, consumer reads row 0 only: every token's K / V still feed the class-token query, so LN1
+                # and the q/k/v projection run on all rows; the attention core runs for ONE query per (sequence,
+                # head), and the out-projection, LN2 and the MLP on the n_seq class-token rows, addressed as strided
+                # views (row stride L * D) of the full-size buffers.  Row-wise identical arithmetic: exact.  The other
+                # rows of O / x1 / x2 are never written nor read.
+                ops.attn_row_fwd(self.qkv[s], self.O[s], self.lse[s], n_seq, L, H, self.causal)
                 oc, x0c, x1c, x2c = (t.view(n_seq, L, D)[:, 0] for t in (self.O[s], x0, x1, x2))
                 gc = self.g[:n_seq]
                 ops.gemm(oc, b.wo, x1c, bias=b.bo, residual=x0c)
@@ -161,6 +162,7 @@ class Tower:
                 ops.gemm(self.hc, b.w1, gc, bias=b.b1, act=ACT_QUICKGELU, out2=self.u[s][:n_seq] if self.save else None)
                 ops.gemm(gc, b.w2, x2c, bias=b.b2, residual=x1c)
                 continue
+            ops.attn_fwd(self.qkv[s], self.O[s], self.lse[s], n_seq, L, H, self.causal)
             ops.gemm(self.O[s], b.wo, x1, bias=b.bo, residual=x0)
             ops.layernorm_fwd(x1, b.ln2_g, b.ln2_b, self.h, mean2, rstd2)
             ops.gemm(self.h, b.w1, self.g, bias=b.b1, act=ACT_QUICKGELU, out2=self.u[s] if self.save else None)
@@ -188,8 +190,9 @@ class Tower:
                 ops.gemm(duc, b.w1_t, self.dhc)
                 ops.gather_ln_bwd(self.dhc, self.X1[i], None, b.ln2_g, mean2[:n_seq], rstd2[:n_seq], dx, n_seq, L, D,
                                   dx_act=self.dxa, dx_in=dx)
-                self.dh.zero_()
+                # d(attention output) of the class-token rows; the one-query backward reads no other row of dh
                 ops.gemm(dxac, b.wo_t, self.dh.view(n_seq, L, D)[:, 0])
+                ops.attn_row_bwd(self.qkv[i], self.dh, self.lse[i], self.dqkv, n_seq, L, H, self.causal)
             else:
                 # MLP branch: x2 = x1 + W2 . gelu(W1 . LN2(x1))
                 ops.gemm(dxa, b.w2_t, self.du, act=ACT_QUICKGELU_GRAD, aux=self.u[i])
@@ -197,7 +200,7 @@ class Tower:
                 ops.layernorm_bwd(self.dh, self.X1[i], b.ln2_g, mean2, rstd2, dx, dx_in=dx, dx_act=self.dxa)
                 # attention branch: x1 = x0 + Wo . attn(Wqkv . LN1(x0))
                 ops.gemm(dxa, b.wo_t, self.dh)
-            ops.attn_bwd(self.qkv[i], self.O[i], self.dh, self.lse[i], self.dqkv, n_seq, L, H, self.causal)
+                ops.attn_bwd(self.qkv[i], self.O[i], self.dh, self.lse[i], self.dqkv, n_seq, L, H, self.causal)
             ops.gemm(self.dqkv, b.wqkv_t, self.dh)
             ops.layernorm_bwd(self.dh, self.X[i], b.ln1_g, mean1, rstd1, dx, dx_in=dx, dx_act=self.dxa)
             if i in self.prompt_layers:

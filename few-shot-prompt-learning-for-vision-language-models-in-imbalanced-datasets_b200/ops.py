@@ -88,6 +88,21 @@ def attn_bwd(qkv, out, dout, lse, dqkv, n_seq, L, H, causal, backend=0):
     return dqkv
 
 
+def attn_row_fwd(qkv, out, lse, n_seq, L, H, causal, idx=None):
+    """One-query attention of a tower's last block: the query is row idx[s] (None: row 0) of every sequence; writes
+    that row of `out` and that entry of `lse` only (psrc_attn_row_fwd)."""
+    cabi.check(cabi.load().psrc_attn_row_fwd(ptr(qkv), ptr(out), ptr(lse), dt(qkv), ptr(idx), n_seq, L, H, int(causal),
+                                             cabi.stream()), "psrc_attn_row_fwd")
+    return out
+
+
+def attn_row_bwd(qkv, dout, lse, dqkv, n_seq, L, H, causal, idx=None):
+    """Backward of attn_row_fwd: reads the query row of `dout`, writes ALL of dqkv (psrc_attn_row_bwd)."""
+    cabi.check(cabi.load().psrc_attn_row_bwd(ptr(qkv), ptr(dout), ptr(lse), ptr(dqkv), dt(qkv), dt(dqkv), ptr(idx),
+                                             n_seq, L, H, int(causal), cabi.stream()), "psrc_attn_row_bwd")
+    return dqkv
+
+
 def im2col_patches(image, patches, R, P):
     B = image.shape[0]
     cabi.check(cabi.load().psrc_im2col_patches(ptr(image), ptr(patches), dt(patches), B, R, P, cabi.stream()),

@@ -121,6 +121,20 @@ int psrc_attn_bwd(const void* qkv, const void* out, const void* dout,
                   int n_seq, int L, int H, int causal, int backend,
                   psrc_stream_t stream);
 
+/* One-query form for the LAST block of a tower: only one row per sequence leaves it
+ * (class token, model.py:426; EOT row, promptsrc.py:64-68), so the attention core
+ * is needed for the query at row idx[s] (idx == NULL: row 0) of each sequence only.
+ * fwd writes that row of out [n_seq*L, D] and that entry of lse [n_seq,H,L]; the
+ * other rows / entries are left untouched.  bwd reads that row of dout and writes
+ * ALL of dqkv (dK, dV of every key <- the one query; dQ zero for every other row).
+ * dtype: F32 / BF16 / F16 (qkv, out); grad_dtype (dout, dqkv): F32 with F32, else BF16. */
+int psrc_attn_row_fwd(const void* qkv, void* out, float* lse, int dtype,
+                      const int32_t* idx, int n_seq, int L, int H, int causal,
+                      psrc_stream_t stream);
+int psrc_attn_row_bwd(const void* qkv, const void* dout, const float* lse, void* dqkv,
+                      int dtype, int grad_dtype, const int32_t* idx,
+                      int n_seq, int L, int H, int causal, psrc_stream_t stream);
+
 /* ------------------------------------------------- token / prompt assembly
  * model.py:401-420 (VisionTransformer.forward up to ln_pre):
  *   im2col: image fp32 [B,3,R,R] -> patches [B*G*G, 3*P*P] (column = c*P*P+ky*P+kx,

@@ -149,7 +149,7 @@ class FakeKernels:
         from psrc_b200 import ops
         monkeypatch.setattr(ops, "_FAKE_KERNELS", True, raising=False)
         for name in ("gemm", "gemm_f32_strided", "layernorm_fwd", "layernorm_bwd", "attn_fwd", "attn_bwd",
-                     "im2col_patches", "assemble_vision_tokens", "assemble_text_prompts", "insert_prompt",
+                     "attn_row_fwd", "attn_row_bwd", "im2col_patches", "assemble_vision_tokens", "assemble_text_prompts", "insert_prompt",
                      "prompt_grad", "gather_ln_fwd", "gather_ln_bwd", "l2norm_fwd", "l2norm_bwd", "loss_fwd_bwd",
                      "sgd_step", "cast", "axpy", "small_linear_fwd", "small_linear_bwd", "group_logits_fwd",
                      "group_logits_bwd", "ctx_bias_grad", "permute_rows"):
@@ -231,6 +231,16 @@ class FakeKernels:
     def attn_bwd(self, qkv, out, dout, lse, dqkv, n_seq, L, H, causal, backend=0):
         self._rec("attn_bwd")
         assert qkv.shape == dqkv.shape == (n_seq * L, 3 * H * 64) and out.shape == dout.shape == (n_seq * L, H * 64)
+        return dqkv
+
+    def attn_row_fwd(self, qkv, out, lse, n_seq, L, H, causal, idx=None):
+        self._rec("attn_row_fwd")
+        assert qkv.shape == (n_seq * L, 3 * H * 64) and out.shape == (n_seq * L, H * 64) and lse.shape == (n_seq, H, L)
+        return out
+
+    def attn_row_bwd(self, qkv, dout, lse, dqkv, n_seq, L, H, causal, idx=None):
+        self._rec("attn_row_bwd")
+        assert qkv.shape == dqkv.shape == (n_seq * L, 3 * H * 64) and dout.shape == (n_seq * L, H * 64)
         return dqkv
 
     def im2col_patches(self, image, patches, R, P):

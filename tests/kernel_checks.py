@@ -544,7 +544,46 @@ def check_fp16_forward(res: Results):
         res.add(tag + " dqkv (bf16)", rel_err(dqkv, qr.grad), 2e-2)
 
 
+def check_attention_row(res: Results):
+    """One-query attention of the last block (psrc_attn_row_fwd / _bwd) against the full attention reference
+    restricted to the query row: vision (row 0, all keys) and text (EOT row, causal), every storage format."""
+    from psrc_b200 import ops
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(13)
+    for (n_seq, L, H, causal, use_idx) in [(5, 201, 12, False, False), (3, 197, 12, False, False), (7, 11, 8, True, True),
+                                           (4, 77, 8, True, True), (2, 259, 16, False, False), (3, 17, 2, False, False),
+                                           (130, 24, 8, True, True), (2, 1, 2, True, True), (3, 33, 2, False, True)]:
+        D = H * 64
+        idx = torch.randint(0, L, (n_seq,), device=dev, generator=g, dtype=torch.int32) if use_idx else None
+        rows = torch.arange(n_seq, device=dev) * L + (idx.long() if use_idx else 0)
+        for dtp, gdt, tol_o, tol_g in ((torch.float32, torch.float32, 2e-6, 2e-5), (torch.bfloat16, torch.bfloat16, 6e-3, 1.2e-2),
+                                       (torch.float16, torch.bfloat16, 1e-3, 6e-3)):
+            qkv = torch.randn(n_seq * L, 3 * D, device=dev, generator=g).to(dtp)
+            qr = qkv.float().clone().requires_grad_(True)
+            o_ref, lse_ref = _attn_ref(qr, n_seq, L, H, causal)
+            out = torch.full((n_seq * L, D), 7.0, device=dev, dtype=dtp)
+            lse = torch.full((n_seq, H, L), 7.0, device=dev)
+            ops.attn_row_fwd(qkv, out, lse, n_seq, L, H, causal, idx=idx)
+            tag = f"attn_row[{str(dtp)[6:]}] n={n_seq} L={L} H={H} causal={int(causal)} idx={int(use_idx)}"
+            res.add(tag + " out (query rows)", rel_err(out[rows], o_ref[rows]), tol_o)
+            pos = rows - torch.arange(n_seq, device=dev) * L
+            ar = torch.arange(n_seq, device=dev)
+            res.add(tag + " lse (query rows)", max_err(lse[ar, :, pos], lse_ref[ar, :, pos]), 1e-4 if dtp == torch.float32 else 2e-2)
+            mask = torch.ones(n_seq * L, dtype=torch.bool, device=dev)
+            mask[rows] = False
+            untouched = bool((out[mask].float() == 7.0).all()) if mask.any() else True
+            res.add(tag + " other rows untouched", 0.0 if untouched else 1.0, 0.0)
+            dout = torch.randn(n_seq * L, D, device=dev, generator=g).to(gdt)     # garbage outside the query rows
+            d_ref = torch.zeros(n_seq * L, D, device=dev)
+            d_ref[rows] = dout[rows].float()
+            o_ref.backward(d_ref)
+            dqkv = torch.full((n_seq * L, 3 * D), float("nan"), device=dev, dtype=gdt)
+            ops.attn_row_bwd(qkv, dout, lse, dqkv, n_seq, L, H, causal, idx=idx)
+            res.add(tag + " dqkv", rel_err(dqkv, qr.grad), tol_g)
+
+
 GROUPS = {
+    "attn_row": check_attention_row,
     "fp16_forward": check_fp16_forward,
     "small_layers": check_small_layers,
     "gemm_simt": lambda r: check_gemm(r, "simt"),

@@ -43,8 +43,10 @@ def test_promptsrc_step_launch_sequence(monkeypatch, prec):
     assert fk.calls.count("attn_fwd") == 3  # frozen teacher: 3 text layers
     step.forward_backward()
     calls = fk.calls[n_teacher:]
-    # 3 towers forward (text, prompted vision, frozen vision) x 3 layers; backward on two of them
-    assert calls.count("attn_fwd") == 9 and calls.count("attn_bwd") == 6
+    # 3 towers forward (text, prompted vision, frozen vision) x 3 layers; backward on two of them.  The LAST block of
+    # the two vision towers runs the one-query attention (only the class token leaves the tower)
+    assert calls.count("attn_fwd") == 7 and calls.count("attn_row_fwd") == 2
+    assert calls.count("attn_bwd") == 5 and calls.count("attn_row_bwd") == 1
     assert calls.count("loss_fwd_bwd") == 1
     # prompt grads: 2 deep text + ctx + 2 deep vision + vpt
     assert calls.count("prompt_grad") == 6
@@ -121,7 +123,8 @@ def test_maple_cocoop_dropins_build_with_reference_names(monkeypatch):
     st.forward_backward()
     calls = fk.calls[n0:]
     assert calls.count("small_linear_fwd") == 1 and calls.count("small_linear_bwd") == 1   # all coupling Linears batched
-    assert calls.count("attn_fwd") == 6 and calls.count("attn_bwd") == 6                   # two towers x 3 layers
+    assert calls.count("attn_fwd") == 5 and calls.count("attn_bwd") == 5                   # two towers x 3 layers,
+    assert calls.count("attn_row_fwd") == 1 and calls.count("attn_row_bwd") == 1           # one-query last vision block
     # CoCoOp: one text pass per image -> B x C sequences in ONE tower launch sequence
     tr2, _, tokens2 = TC.make_trainer("CoCoOp", "fp32", device="cpu")
     assert tr2.get_model_names() == ["prompt_learner"]
@@ -133,7 +136,8 @@ def test_maple_cocoop_dropins_build_with_reference_names(monkeypatch):
     st2.forward_backward()
     calls = fk.calls[n0:]
     assert calls.count("small_linear_fwd") == 2 and calls.count("small_linear_bwd") == 2   # meta-net
-    assert calls.count("attn_fwd") == 6 and calls.count("attn_bwd") == 3                   # vision fwd only, text fwd+bwd
+    assert calls.count("attn_fwd") == 5 and calls.count("attn_row_fwd") == 1               # vision fwd only (last block
+    assert calls.count("attn_bwd") == 3                                                    # one-query), text fwd+bwd
     assert calls.count("prompt_grad") == TC.B and calls.count("ctx_bias_grad") == 1
     assert calls.count("group_logits_fwd") == 1 and calls.count("group_logits_bwd") == 1
 

@@ -52,7 +52,8 @@ def _fp16(x):
 
 
 class TorchKernels:
-    NAMES = ("gemm", "gemm_f32_strided", "layernorm_fwd", "layernorm_bwd", "attn_fwd", "attn_bwd", "im2col_patches",
+    NAMES = ("gemm", "gemm_f32_strided", "layernorm_fwd", "layernorm_bwd", "attn_fwd", "attn_bwd", "attn_row_fwd",
+             "attn_row_bwd", "im2col_patches",
              "assemble_vision_tokens", "assemble_text_prompts", "insert_prompt", "prompt_grad", "gather_ln_fwd",
              "gather_ln_bwd", "l2norm_fwd", "l2norm_bwd", "loss_fwd_bwd", "sgd_step", "cast", "axpy",
              "small_linear_fwd", "small_linear_bwd", "group_logits_fwd", "group_logits_bwd", "ctx_bias_grad", "permute_rows")
@@ -123,6 +124,28 @@ class TorchKernels:
             q = qkv.detach().float().clone().requires_grad_(True)
             o, _ = _attn(q, n_seq, L, H, causal)
             o.backward(dout.float())
+        dqkv.copy_(q.grad)
+        return dqkv
+
+    @classmethod
+    def attn_row_fwd(cls, qkv, out, lse, n_seq, L, H, causal, idx=None):
+        """Contract of psrc_attn_row_fwd: only the query row of `out` / entry of `lse` is written."""
+        o, l = _attn(qkv, n_seq, L, H, causal)
+        r = cls._rows(idx, n_seq, L)
+        out[r] = o[r].to(out.dtype)
+        pos = (r - torch.arange(n_seq) * L)
+        lse[torch.arange(n_seq), :, pos] = l[torch.arange(n_seq), :, pos]
+        return out
+
+    @classmethod
+    def attn_row_bwd(cls, qkv, dout, lse, dqkv, n_seq, L, H, causal, idx=None):
+        r = cls._rows(idx, n_seq, L)
+        d = torch.zeros(n_seq * L, H * 64)
+        d[r] = dout[r].float()                   # only the query row of dout is read
+        with torch.enable_grad():
+            q = qkv.detach().float().clone().requires_grad_(True)
+            o, _ = _attn(q, n_seq, L, H, causal)
+            o.backward(d)
         dqkv.copy_(q.grad)
         return dqkv
 
