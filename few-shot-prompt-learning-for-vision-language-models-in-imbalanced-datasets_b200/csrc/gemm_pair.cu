@@ -76,7 +76,30 @@ struct Params {
   // 16-bit formats (0 = bf16, 1 = fp16): A / W operands, the 16-bit output(s), the QuickGELU' aux operand.  fp16
   // forward operands carry 3 more mantissa bits than bf16 at the same tensor-core rate ("fp16 forward")
   int ab_f16, out_f16, out2_f16, aux_f16;
+  // Tail split (wave quantisation): work items [0, n_full) are whole 256 x BN tiles; every remaining tile is cut
+  // along N into `split` items of 256 x (BN / split), so the last, partially filled round of the persistent loop
+  // occupies split x as many CTA pairs for a fraction of a tile time each.  split = 1: no tail items.
+  int n_full, split, items;
 };
+
+struct Item {
+  int m_blk, col0, bn;
+};
+template <int BN>
+__device__ __forceinline__ Item decode_item(int w, const Params& p) {
+  Item it;
+  int tile = w, sub = 0;
+  it.bn = BN;
+  if (w >= p.n_full) {
+    const int t = w - p.n_full;
+    tile = p.n_full + t / p.split;
+    sub = t % p.split;
+    it.bn = BN / p.split;
+  }
+  it.m_blk = tile / p.tiles_n;
+  it.col0 = (tile % p.tiles_n) * BN + sub * it.bn;
+  return it;
+}
 
 __device__ __forceinline__ uint32_t pack16(float lo, float hi, int f16) {
   if (f16) {
@@ -101,14 +124,13 @@ __device__ __forceinline__ uint32_t sw_chunk(int r, int j) {
 template <int BN, int STAGES, int MODE, int OUT_BYTES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                 const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_out2,
-                 const __grid_constant__ CUtensorMap tmap_in, Params p) {
+                 const __grid_constant__ CUtensorMap tmap_w_tail, const __grid_constant__ CUtensorMap tmap_out,
+                 const __grid_constant__ CUtensorMap tmap_out2, const __grid_constant__ CUtensorMap tmap_in, Params p) {
   constexpr bool kHasIn = (MODE == kGeluGrad || MODE == kResidual);
   constexpr int kIn = kHasIn ? kInSlots : 0;   // epilogues without a second operand give the ring's 64 KB to the pipeline
   using S = Smem<BN, STAGES, kIn, (MODE == kResidual) ? 128 * 128 : 128 * 64>;   // fp32 residual / bf16 aux chunk
   constexpr int kInRowBytes = (MODE == kResidual) ? 128 : 64;
   constexpr int kOutRowBytes = 32 * OUT_BYTES;
-  constexpr int kChunks = BN / 32;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOffset);
@@ -125,12 +147,12 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int pair_id = blockIdx.x >> 1;
   const int n_pairs = gridDim.x >> 1;
   const int num_kb = (p.K + kBK - 1) / kBK;
-  const int num_tiles = p.tiles_m * p.tiles_n;
   constexpr uint32_t kTmemCols = 2 * BN > 256 ? 512 : 256;   // two accumulator stages, power-of-two allocation
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_w);
+    if (p.split > 1) tma_prefetch_desc(&tmap_w_tail);
     tma_prefetch_desc(&tmap_out);
     if (MODE == kGelu) tma_prefetch_desc(&tmap_out2);
     if (kHasIn) tma_prefetch_desc(&tmap_in);
@@ -164,17 +186,19 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = pair_id; tile < num_tiles; tile += n_pairs) {
-        const int m_blk = tile / p.tiles_n, n_blk = tile % p.tiles_n;
-        const int row_a = m_blk * 256 + (int)rank * kBMcta;
-        const int row_w = n_blk * BN + (int)rank * (BN / 2);
+      for (int w = pair_id; w < p.items; w += n_pairs) {
+        const Item it = decode_item<BN>(w, p);
+        const int row_a = it.m_blk * 256 + (int)rank * kBMcta;
+        const int row_w = it.col0 + (int)rank * (it.bn / 2);
+        const CUtensorMap* tw = it.bn == BN ? &tmap_w : &tmap_w_tail;   // box of bn / 2 rows of W per CTA
+        const uint32_t bytes = 2u * (uint32_t)(S::kABytes + (it.bn / 2) * kBK * 2);
         for (int kb = 0; kb < num_kb; ++kb) {
           wait_bounded(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * S::kStageBytes;
           uint8_t* sb = sa + S::kABytes;
-          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * S::kStageBytes);
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], bytes);
           tma_load_2d_pair(&tmap_a, &full_bar[stage], sa, kb * kBK, row_a);
-          tma_load_2d_pair(&tmap_w, &full_bar[stage], sb, kb * kBK, row_w);
+          tma_load_2d_pair(tw, &full_bar[stage], sb, kb * kBK, row_w);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -183,13 +207,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // ===================== MMA issuer (leader CTA, one thread) =====================
     if (rank == 0 && lane == 0) {
       // instruction descriptor: D=f32, A=B=bf16 (format 1) or fp16 (format 0), both K-major, N = BN, M = 256 (pair)
-      const uint32_t idesc = (1u << 4) | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10))) | ((uint32_t)(BN >> 3) << 17) |
-                             ((uint32_t)(256 >> 4) << 24);
+      const uint32_t idesc0 = (1u << 4) | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10))) | ((uint32_t)(256 >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int tile = pair_id; tile < num_tiles; tile += n_pairs) {
+      for (int w = pair_id; w < p.items; w += n_pairs) {
+        const uint32_t idesc = idesc0 | ((uint32_t)(decode_item<BN>(w, p).bn >> 3) << 17);   // N = bn
         wait_bounded(&tmem_empty[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
@@ -216,11 +240,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (kHasIn && lane == 0) {
       int slot = 0;
       uint32_t phase = 0;
-      for (int tile = pair_id; tile < num_tiles; tile += n_pairs) {
-        const int m_blk = tile / p.tiles_n, n_blk = tile % p.tiles_n;
-        const int row0 = m_blk * 256 + (int)rank * kBMcta;
-        for (int c = 0; c < kChunks; ++c) {
-          const int col0 = n_blk * BN + c * 32;
+      for (int w = pair_id; w < p.items; w += n_pairs) {
+        const Item it = decode_item<BN>(w, p);
+        const int row0 = it.m_blk * 256 + (int)rank * kBMcta;
+        for (int c = 0; c < it.bn / 32; ++c) {
+          const int col0 = it.col0 + c * 32;
           if (col0 >= p.N) break;
           wait_bounded(&in_empty[slot], phase ^ 1);
           mbar_expect_tx(&in_full[slot], 128 * kInRowBytes);
@@ -238,16 +262,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     int as = 0;
     uint32_t aphase = 0;
     uint32_t gbase = 0;                     // chunks the prefetch warp has issued before this tile (ring position)
-    for (int tile = pair_id; tile < num_tiles; tile += n_pairs) {
-      const int m_blk = tile / p.tiles_n, n_blk = tile % p.tiles_n;
-      const int row0 = m_blk * 256 + (int)rank * kBMcta + q * 32;   // first row of this warp's 32-row box
+    for (int w = pair_id; w < p.items; w += n_pairs) {
+      const Item it = decode_item<BN>(w, p);
+      const int row0 = it.m_blk * 256 + (int)rank * kBMcta + q * 32;   // first row of this warp's 32-row box
       wait_bounded(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
-      const int tile_chunks = min(kChunks, (p.N - n_blk * BN + 31) >> 5);
+      const int tile_chunks = max(0, min(it.bn / 32, (p.N - it.col0 + 31) >> 5));
 #pragma unroll 1
       for (int c = par; c < tile_chunks; c += 2) {
-        const int col0 = n_blk * BN + c * 32;
+        const int col0 = it.col0 + c * 32;
         uint32_t r[32];
         tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
         float v[32];
@@ -405,6 +429,31 @@ static int sm_count() {
   return n;
 }
 
+// How finely to cut the tiles of the last, partially filled round (rem = tiles % pairs of them) along N.  A 256 x bn
+// item re-reads the whole 256-row A tile, so its cost is not bn / BN of a tile: the shared-memory-bandwidth model of
+// DESIGN 4 (A and W both written by TMA and read by the MMA) gives (32 + 2 * 16 * bn / 256) / 64 of a full tile per
+// k-block: 0.75 at bn = 128, 0.625 at bn = 64, plus the fixed per-item prologue / epilogue.  Pick the split whose
+// extra rounds cost least; PSRC_PAIR_SPLIT = 1 / 2 / 4 forces it (tuning knob).
+static int tail_split(int tiles, int pairs, int BN) {
+  static const int force = getenv("PSRC_PAIR_SPLIT") ? atoi(getenv("PSRC_PAIR_SPLIT")) : 0;
+  const int rem = tiles % pairs;
+  if (rem == 0) return 1;
+  if (force == 1 || force == 2 || force == 4) return (BN / force >= 64) ? force : 1;
+  const float cost[3] = {1.0f, 0.80f, 0.70f};
+  int best = 1;
+  float best_cost = 1.0f;   // split 1: one more full round
+  for (int i = 1; i < 3; ++i) {
+    const int sp = 1 << i;
+    if (BN / sp < 64) break;
+    const float c = (float)((rem * sp + pairs - 1) / pairs) * cost[i];
+    if (c < best_cost - 0.05f) {
+      best_cost = c;
+      best = sp;
+    }
+  }
+  return best;
+}
+
 template <int BN, int STAGES, int MODE, int OUT_BYTES>
 static int launch(const psrc_gemm_args& a, cudaStream_t stream) {
   using S = Smem<BN, STAGES, (MODE == kGeluGrad || MODE == kResidual) ? kInSlots : 0, (MODE == kResidual) ? 128 * 128 : 128 * 64>;
@@ -415,10 +464,23 @@ static int launch(const psrc_gemm_args& a, cudaStream_t stream) {
     PSRC_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kDyn));
     attr_set = true;
   }
-  CUtensorMap ta, tw, to, to2, tin;
+  Params p;
+  p.M = a.M; p.N = a.N; p.K = a.K;
+  p.tiles_m = (a.M + 255) / 256;
+  p.tiles_n = (a.N + BN - 1) / BN;
+  const int tiles = p.tiles_m * p.tiles_n, max_pairs = sm_count() / 2;
+  p.split = tail_split(tiles, max_pairs, BN);
+  const int rem = tiles % max_pairs;
+  p.n_full = p.split > 1 ? tiles - rem : tiles;
+  p.items = p.n_full + (tiles - p.n_full) * p.split;
+  CUtensorMap ta, tw, twt, to, to2, tin;
   int rc;
   if ((rc = make_map(&ta, a.A, a.ab_dtype, a.M, a.K, a.lda, kBK, kBMcta, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = make_map(&tw, a.W, a.ab_dtype, a.N, a.K, a.ldw, kBK, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  twt = tw;
+  if (p.split > 1)
+    if ((rc = make_map(&twt, a.W, a.ab_dtype, a.N, a.K, a.ldw, kBK, BN / p.split / 2, CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
   const CUtensorMapSwizzle osw = OUT_BYTES == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   if ((rc = make_map(&to, a.out, a.out_dtype, a.M, a.N, a.ldo, 32, 32, osw))) return rc;
   to2 = to;
@@ -429,10 +491,6 @@ static int launch(const psrc_gemm_args& a, cudaStream_t stream) {
     if ((rc = make_map(&tin, a.residual, PSRC_F32, a.M, a.N, a.ldres, 32, 128, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if (MODE == kGeluGrad)
     if ((rc = make_map(&tin, a.aux, a.aux_dtype, a.M, a.N, a.ldaux, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
-  Params p;
-  p.M = a.M; p.N = a.N; p.K = a.K;
-  p.tiles_m = (a.M + 255) / 256;
-  p.tiles_n = (a.N + BN - 1) / BN;
   p.bias = a.bias;
   p.alpha = a.alpha;
   p.has_out2 = (MODE == kGelu && a.out2) ? 1 : 0;
@@ -440,13 +498,13 @@ static int launch(const psrc_gemm_args& a, cudaStream_t stream) {
   p.out_f16 = a.out_dtype == PSRC_F16;
   p.out2_f16 = a.out2_dtype == PSRC_F16;
   p.aux_f16 = a.aux_dtype == PSRC_F16;
-  const int pairs = std::min(p.tiles_m * p.tiles_n, sm_count() / 2);
+  const int pairs = std::min(p.items, max_pairs);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * pairs);
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = S::kDyn;
   cfg.stream = stream;
-  PSRC_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kernel, ta, tw, to, to2, tin, p));
+  PSRC_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kernel, ta, tw, twt, to, to2, tin, p));
   count_launch();
   return PSRC_OK;
 }
