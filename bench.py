@@ -367,7 +367,7 @@ def flop_model(args, arch, step, B, Lt):
     zs, vb = step.cfg.zero_shot_branch, ncv > 0
     fl = flops.step_flops(arch, B, n_text, Lt, ncv, zs, vb)
     dense = flops.step_flops(arch, B, n_text, 77, ncv, zs, vb)
-    shapes = flops.gemm_launches(arch, B, n_text, Lt, ncv, zs, vb, vision_cls_rows=(B if not vb else 0))
+    shapes = flops.gemm_launches(arch, B, n_text, Lt, ncv, zs, vb, vision_cls_rows=B)
     _ = tr
     return fl, dense, shapes
 
@@ -484,9 +484,10 @@ def b200_arm(args):
     step.train_step()
     torch.cuda.synchronize()
     launches = cabi.launch_count() - n0
-    # multi-GPU: eager by default -- capturing the NCCL collectives was measured at N=2 (24.47 vs 24.57 ms/step: the
-    # step is not launch-bound) and the captured communicator did not shut down cleanly, so it stays opt-in
-    use_graph = not args.no_graph and (world == 1 or args.graph_multi)
+    # multi-GPU: the segments between two collectives are captured as CUDA graphs, the NCCL calls stay outside of them
+    # and are issued asynchronously (step.run_segments): no launch overhead on the small text shards, no NCCL inside
+    # a graph (a captured communicator did not shut down cleanly in round 1)
+    use_graph = not args.no_graph
     if use_graph:
         step.capture(warmup=1)
 
@@ -556,6 +557,9 @@ def b200_arm(args):
             sstep, _ = build_step(args, Bs, world, rank, pg, dev)
             sstep.image.copy_(image_host[:Bs])
             sstep.labels.copy_(label_host[:Bs].to(torch.int32))
+            sstep.train_step()
+            if use_graph:
+                sstep.capture(warmup=1)
             for _ in range(3):
                 sstep.run()
             ms_s = timed(sstep.run, args.steps)

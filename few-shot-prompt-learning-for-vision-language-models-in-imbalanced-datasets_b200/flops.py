@@ -15,18 +15,25 @@ def block_bwd(n, L, D):
     return n * L * (24 * D * D + 8 * L * D)
 
 
+def last_block_saving(n, L, D, attn_coeff):
+    """FLOPs NOT executed in a tower's last block when only row 0 of every sequence is consumed."""
+    return n * (L - 1) * (18 * D * D + attn_coeff * L * D)
+
+
 def step_flops(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward, text_backward=True):
     """Executed FLOPs of one train step on one rank (B local images, C local classes, Lt text positions)."""
     Dv, Dt, E, P = arch.vision_width, arch.transformer_width, arch.embed_dim, arch.n_patches
     Lv = 1 + P + n_ctx_vision
     out = {}
     out["patch_embed"] = 2 * B * P * (3 * arch.vision_patch_size ** 2) * Dv
-    out["vision_fwd"] = arch.vision_layers * block_fwd(B, Lv, Dv)
-    if not vision_backward:   # forward-only prompted tower (CoOp / CoCoOp): last MLP on the class-token rows only
-        out["vision_fwd"] -= B * (Lv - 1) * 16 * Dv * Dv
-    out["vision_bwd"] = arch.vision_layers * block_bwd(B, Lv, Dv) if vision_backward else 0
-    # (the frozen tower's last block runs its MLP on the class-token rows only: 16 D^2 per skipped row)
-    out["frozen_vision_fwd"] = (arch.vision_layers * block_fwd(B, 1 + P, Dv) - B * P * 16 * Dv * Dv) if zero_shot else 0
+    # The LAST block of every vision tower runs LN1 + the q/k/v projection on all rows, the attention core for ONE
+    # query per (sequence, head) and the out-projection + MLP on the class-token rows only (engine.Tower
+    # .cls_only_last_mlp): per skipped row 18 D^2 of GEMM and 4 L D (forward) / 8 L D (backward) of attention less.
+    out["vision_fwd"] = arch.vision_layers * block_fwd(B, Lv, Dv) - last_block_saving(B, Lv, Dv, 4)
+    out["vision_bwd"] = (arch.vision_layers * block_bwd(B, Lv, Dv) - last_block_saving(B, Lv, Dv, 8)) \
+        if vision_backward else 0
+    out["frozen_vision_fwd"] = (arch.vision_layers * block_fwd(B, 1 + P, Dv) - last_block_saving(B, 1 + P, Dv, 4)) \
+        if zero_shot else 0
     out["text_fwd"] = arch.transformer_layers * block_fwd(C, Lt, Dt)
     out["text_bwd"] = arch.transformer_layers * block_bwd(C, Lt, Dt) if text_backward else 0
     heads = 2 * B * Dv * E * (2 if zero_shot else 1) + 2 * C * Dt * E
@@ -63,17 +70,19 @@ def gemm_launches(arch, B, C, Lt, n_ctx_vision, zero_shot, vision_backward, visi
 
     def tower(M, D, layers, bwd, cls_rows=0):
         res, gelu = ("res", "gelu_save") if bwd else ("res_inplace", "gelu")
-        mlp_layers = layers - 1 if cls_rows else layers        # forward-only vision tower: last MLP on class-token rows
-        out.extend([(M, 3 * D, D, layers, "none"), (M, D, D, layers, res), (M, 4 * D, D, mlp_layers, gelu),
-                    (M, D, 4 * D, mlp_layers, res)])
+        full = layers - 1 if cls_rows else layers      # vision towers: the last block's out-projection / MLP (and
+        out.extend([(M, 3 * D, D, layers, "none"), (M, D, D, full, res), (M, 4 * D, D, full, gelu),   # their dgrads)
+                    (M, D, 4 * D, full, res)])                                          # run on class-token rows
         if cls_rows:
-            out.extend([(cls_rows, 4 * D, D, 1, gelu), (cls_rows, D, 4 * D, 1, res)])
+            out.extend([(cls_rows, D, D, 1, res), (cls_rows, 4 * D, D, 1, gelu), (cls_rows, D, 4 * D, 1, res)])
         if bwd:
-            out.extend([(M, 4 * D, D, layers, "gelugrad"), (M, D, 4 * D, layers, "none"), (M, D, D, layers, "none"),
+            out.extend([(M, 4 * D, D, full, "gelugrad"), (M, D, 4 * D, full, "none"), (M, D, D, full, "none"),
                         (M, D, 3 * D, layers, "none")])
+            if cls_rows:
+                out.extend([(cls_rows, 4 * D, D, 1, "gelugrad"), (cls_rows, D, 4 * D, 1, "none"),
+                            (cls_rows, D, D, 1, "none")])
 
-    tower(B * (1 + P + n_ctx_vision), Dv, arch.vision_layers, vision_backward,
-          cls_rows=0 if vision_backward else vision_cls_rows)
+    tower(B * (1 + P + n_ctx_vision), Dv, arch.vision_layers, vision_backward, cls_rows=vision_cls_rows)
     if zero_shot:
         tower(B * (1 + P), Dv, arch.vision_layers, False, cls_rows=B)
     tower(C * Lt, Dt, arch.transformer_layers, True)

@@ -214,7 +214,6 @@ class PromptedClipStep:
         if self.text_perm is not None:
             self.x0_end, self.dx0_end = e(self.Cl * self.Lt, self.Dt), e(self.Cl * self.Lt, self.Dt)
             self.zero_pos = torch.zeros_like(self.tpos)
-        self.losses = e(4)
         self.losses_host = torch.zeros(4, dtype=torch.float32).pin_memory() if dev.type == "cuda" else torch.zeros(4)
         self._text_ahead = False     # True: the text-tower prefix of the NEXT step is already enqueued (graphs only)
         self.loss_scratch = e(4 * B + 2 * 296)
@@ -266,7 +265,10 @@ class PromptedClipStep:
             self.param_shapes.update({"meta.w1": (Hm, self.E), "meta.b1": (Hm,), "meta.w2": (self.Dt, Hm),
                                       "meta.b2": (self.Dt,)})
         n = sum(math.prod(s) for s in self.param_shapes.values())
-        self.flat_param, self.flat_grad = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+        # gradients and the 4 loss terms live in ONE buffer: multi-GPU runs sum both with a single all-reduce
+        self.flat_grad_ext = torch.zeros(n + 4, device=dev)
+        self.flat_param, self.flat_grad = torch.zeros(n, device=dev), self.flat_grad_ext[:n]
+        self.losses = self.flat_grad_ext[n:]
         self.params, self.grads, self.param_offsets, off = {}, {}, {}, 0
         for k, s in self.param_shapes.items():
             m = math.prod(s)
@@ -312,8 +314,8 @@ class PromptedClipStep:
         ops.gather_ln_fwd(tower.x_final, None, *self.ln_post, hv, *stats, tower.n_seq, tower.L, self.Dv)  # :426
         ops.gemm(hv, self.vproj_t, f_out)                                    # :428-429
 
-    def text_features(self, ctx=None):
-        """Normalised text features of this rank's class shard -> self.t_hat_l (and self.t_hat)."""
+    def text_features(self, ctx=None, gather=True):
+        """Normalised text features of this rank's class shard -> self.t_hat_l (and, gathered, self.t_hat)."""
         cfg = self.cfg
         ctx = self.params["ctx"] if ctx is None else ctx
         if cfg.ctx_per_class:
@@ -339,7 +341,7 @@ class PromptedClipStep:
                           self.Lt, self.Dt)                                  # promptsrc.py:64-68
         ops.gemm(self.ht, self.tproj_t, self.t)
         ops.l2norm_fwd(self.t, self.t_hat_l, self.t_inv)                     # promptsrc.py:191
-        if self.share_text:
+        if self.share_text and gather:
             dist.all_gather_into_tensor(self.t_hat, self.t_hat_l, group=cfg.process_group)
         return self.t_hat
 
@@ -389,6 +391,17 @@ class PromptedClipStep:
             self.text_features()
 
     def forward_rest(self):
+        self._forward_vision()
+        return self._forward_logits()
+
+    def _forward_logits(self):
+        if self.per_image:                 # the context shift needs the image features first (cocoop.py:241-246)
+            self.text_features()
+        return self.compute_logits()
+
+    def _forward_vision(self):
+        """Everything of the forward that needs the images but not the (gathered) text features: both vision towers,
+        image features and -- PromptSRC -- the teacher logits."""
         cfg = self.cfg
         B, C, E = cfg.batch, cfg.n_cls, self.E
         side = self._side_stream() if (cfg.zero_shot_branch and self.overlap_zero_shot) else None
@@ -406,16 +419,12 @@ class PromptedClipStep:
                 ops.gemm_f32_strided(B, C, E, self.zf_hat, E, 1, self.fixed_hat_h, E, 1, self.zs_logits,
                                      alpha=self.scale)                      # promptsrc.py:201
             self.image_features(embed=False)
-        if self.per_image:                 # the context shift needs the image features first (cocoop.py:241-246)
-            self.text_features()
-        self.compute_logits()
         if side is not None:
             torch.cuda.current_stream().wait_stream(side)
         elif cfg.zero_shot_branch:
             self.zero_shot_features()
             ops.gemm_f32_strided(B, C, E, self.zf_hat, E, 1, self.fixed_hat_h, E, 1, self.zs_logits,
                                  alpha=self.scale)                          # promptsrc.py:201
-        return self.logits
 
     overlap_zero_shot = True     # measured on B200 at cfg 3: 24.03 -> 23.47 ms/step
 
@@ -440,11 +449,16 @@ class PromptedClipStep:
 
     def backward_after_text(self):
         """Everything of the step that needs the image batch: vision towers, logits, losses, prompt-only backward."""
-        cfg = self.cfg
-        C = cfg.n_cls
-        zs = cfg.zero_shot_branch
         self.forward_rest()
-        multi = cfg.world_size > 1
+        self._loss()
+        self.backward_from_buffers(feature_grads=self.cfg.zero_shot_branch, reduce=False)
+        if self.cfg.world_size > 1:        # prompt gradients and the 4 loss terms in one message
+            dist.all_reduce(self.flat_grad_ext, group=self.cfg.process_group)
+        return self.losses
+
+    def _loss(self):
+        cfg = self.cfg
+        zs = cfg.zero_shot_branch
         d_that_l1 = self.d_that_l1 if self.share_text else self.d_that_l
         ops.loss_fwd_bwd(self.logits, self.labels, self.d_logits, self.losses, self.loss_scratch,
                          zs_logits=self.zs_logits if zs else None, focal_alpha=self.focal_alpha,
@@ -455,13 +469,72 @@ class PromptedClipStep:
                          f_hat=self.f_hat if zs else None, f_zs=self.zf_hat if zs else None,
                          d_fhat=self.d_fhat if zs else None,
                          w_kl=cfg.w_logits, w_text=cfg.w_text, w_image=cfg.w_image,
-                         B_global=self.B_global, Ct_global=C)
-        self.backward_from_buffers(feature_grads=zs)
-        if multi:
-            dist.all_reduce(self.losses, group=cfg.process_group)
+                         B_global=self.B_global, Ct_global=cfg.n_cls)
+
+    # ------------------------------------------------------------------ multi-GPU: segments between the collectives
+    # world_size > 1: the step is cut where a collective sits, each segment is a CUDA graph (no NCCL call
+    # inside a graph), and the collectives are issued asynchronously so that they run under independent compute:
+    #   seg 0  text tower forward (own class shard)            -> all-gather t_hat        | runs under seg 1
+    #   seg 1  vision towers forward (+ frozen tower)            (needs the images, not t_hat)
+    #   seg 2  logits, fused loss, dL/dt_hat partial sums      -> reduce-scatter          | runs under seg 3
+    #   seg 3  vision backward                                   (needs d_logits, t_hat -- not the scattered sum)
+    #   seg 4  text backward (+ MaPLe coupling backward)       -> ONE all-reduce: flat prompt gradient + 4 loss terms
+    #   seg 5  SGD
+    # CoCoOp (pure batch sharding): seg 0 = the whole forward + backward, all-reduce, seg 1 = SGD.
+    def _segments(self):
+        zs = self.cfg.zero_shot_branch
+        if not self.share_text:
+            def whole():
+                self.forward_text()
+                self.forward_rest()
+                self._loss()
+                self.backward_from_buffers(feature_grads=zs, reduce=False)
+            return [whole, self.sgd]
+
+        def seg_text_fwd():
+            self._text_ahead = False
+            self.text_features(gather=False)
+
+        def seg_logits_loss():
+            self._forward_logits()
+            self._loss()
+            self._backward_text_pre()
+
+        def seg_text_bwd():
+            self._backward_text_post(zs)
+            self._backward_coupling()
+        return [seg_text_fwd, self._forward_vision, seg_logits_loss, lambda: self._backward_vision(zs), seg_text_bwd,
+                self.sgd]
+
+    def run_segments(self, graphs=None, wait_event=None):
+        """One train step at world_size > 1.  graphs: the captured segments (capture()), None = eager launches."""
+        pg = self.cfg.process_group
+        segs = self._segments()
+        run = (lambda i: graphs[i].replay()) if graphs is not None else (lambda i: segs[i]())
+        main = torch.cuda.current_stream() if self.device.type == "cuda" else None
+        if not self.share_text:
+            if wait_event is not None:
+                main.wait_event(wait_event)
+            run(0)
+            dist.all_reduce(self.flat_grad_ext, group=pg)
+            run(1)
+            return self.losses
+        run(0)
+        w_ag = dist.all_gather_into_tensor(self.t_hat, self.t_hat_l, group=pg, async_op=True)
+        if wait_event is not None:
+            main.wait_event(wait_event)         # the batch's host-to-device copy (run_host)
+        run(1)
+        w_ag.wait()
+        run(2)
+        w_rs = dist.reduce_scatter_tensor(self.d_that_l, self.d_that_full, group=pg, async_op=True)
+        run(3)
+        w_rs.wait()
+        run(4)
+        dist.all_reduce(self.flat_grad_ext, group=pg)
+        run(5)
         return self.losses
 
-    def backward_from_buffers(self, feature_grads: bool):
+    def backward_from_buffers(self, feature_grads: bool, reduce: bool = True):
         """Prompt-only backward from d(loss)/d(logits) in self.d_logits.  feature_grads: the direct gradients
         w.r.t. the normalised features (PromptSRC's L1 terms, or an autograd caller's) are already in
         self.d_fhat and self.d_that_l (single GPU) / self.d_that_l1 (sharded) and are added to the logits part.
@@ -481,31 +554,44 @@ class PromptedClipStep:
                 self._backward_text(feature_grads)
             self._backward_vision(feature_grads)
             main.wait_stream(side)
-        if cfg.coupling:
+        self._backward_coupling()
+        if multi and reduce:
+            dist.all_reduce(self.flat_grad, group=cfg.process_group)
+        return self.flat_grad
+
+    def _backward_coupling(self):
+        if self.cfg.coupling:
             # d(text prompts) += d(vision prompts) . W ; dW, db of the coupling Linears (autograd of maple.py:199-204)
             ops.small_linear_bwd(self.couple_x, self.couple_w, self.vis_prompt_grad, dx=self.couple_dx,
                                  dw=self.couple_dw, db=self.couple_db, accumulate_dx=True)
-        if multi:
-            dist.all_reduce(self.flat_grad, group=cfg.process_group)
-        return self.flat_grad
 
     overlap_backward = False     # measured: no gain (22.98 vs 23.09 ms), kept as a switch
 
     def _backward_text(self, zs: bool):
+        self._backward_text_pre(zs)
+        if self.share_text:
+            dist.reduce_scatter_tensor(self.d_that_l, self.d_that_full, group=self.cfg.process_group)
+        self._backward_text_post(zs)
+
+    def _backward_text_pre(self, zs: bool = False):
+        """dL/dt_hat = s * dlogits^T f_hat (+ direct part): with a sharded text tower the partial sum over this
+        rank's images for ALL classes (input of the reduce-scatter), else the complete gradient."""
         cfg = self.cfg
         B, C, E = cfg.batch, cfg.n_cls, self.E
-        # ---- text side: dL/dt_hat = s * dlogits^T f_hat (+ direct part)
         if self.per_image:
             assert not zs
             ops.group_logits_bwd(self.f_hat, self.d_logits, self.d_that_l, self.scale)
         elif self.share_text:
             ops.gemm_f32_strided(C, E, B, self.d_logits, 1, C, self.f_hat, 1, E, self.d_that_full[:C], alpha=self.scale)
-            dist.reduce_scatter_tensor(self.d_that_l, self.d_that_full, group=cfg.process_group)
-            if zs:
-                ops.axpy(self.d_that_l, self.d_that_l1, 1.0)
         else:
             ops.gemm_f32_strided(C, E, B, self.d_logits, 1, C, self.f_hat, 1, E, self.d_that_l, alpha=self.scale,
                                  beta=1.0 if zs else 0.0)
+
+    def _backward_text_post(self, zs: bool):
+        cfg = self.cfg
+        B = cfg.batch
+        if self.share_text and zs:
+            ops.axpy(self.d_that_l, self.d_that_l1, 1.0)       # + the L1-text gradient of the own shard
         ops.l2norm_bwd(self.d_that_l, self.t_hat_l, self.t_inv, self.dt_)
         if self.dt_a is not self.dt_:
             ops.cast(self.dt_, self.dt_a)
@@ -625,7 +711,10 @@ class PromptedClipStep:
         ops.sgd_step(self.flat_param, self.flat_grad, self.mom_buf, self.lr_dev, m, d, wd, False, False)
 
     def train_step(self):
-        """forward + losses + prompt-only backward + SGD on the resident inputs (self.image / self.labels)."""
+        """forward + losses + prompt-only backward + SGD on the resident inputs (self.image / self.labels).
+        world_size > 1: the overlapped segment order of `run_segments`, launched eagerly."""
+        if self.cfg.world_size > 1:
+            return self.run_segments(None)
         self.forward_backward()
         self.sgd()
         return self.losses
@@ -640,8 +729,10 @@ class PromptedClipStep:
 
     def capture(self, warmup: int = 2):
         """Capture train_step into CUDA graphs (shapes are static; every kernel is stateless).  With world_size > 1
-        the three NCCL collectives of the step are captured with it (every rank must call capture() at the same
-        point, after at least one eager step has initialised the communicator)."""
+        every segment between two collectives becomes one graph and the NCCL calls stay outside (`run_segments`);
+        every rank must call capture() at the same point."""
+        if self.cfg.world_size > 1:
+            return self._capture_segments(warmup)
         keep = (self.flat_param.clone(), self.mom_buf.clone())
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
@@ -662,6 +753,25 @@ class PromptedClipStep:
         self._graph = (g0, g1)
         self._text_ahead = False
         return self._graph
+
+    def _capture_segments(self, warmup: int = 1):
+        keep = (self.flat_param.clone(), self.mom_buf.clone())
+        for _ in range(max(1, warmup)):                 # eager: initialises NCCL, fills every buffer with valid data
+            self.run_segments(None)
+        torch.cuda.synchronize()
+        graphs, pool = [], None
+        for fn in self._segments():                     # each segment replays the SAME launches on the same buffers
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, pool=pool):
+                fn()
+            pool = pool or g.pool()
+            graphs.append(g)
+        self.flat_param.copy_(keep[0])
+        self.mom_buf.copy_(keep[1])
+        self._seg_graphs = graphs
+        self._graph = None
+        self._text_ahead = False
+        return graphs
 
     # The text-tower prefix reads only the prompt parameters, so as soon as one step's SGD is enqueued the NEXT step's
     # prefix can follow it on the stream: it then runs while the host is still waiting for this step's loss, logging
@@ -701,6 +811,8 @@ class PromptedClipStep:
 
     def run(self):
         """One train step on the resident inputs: graph replay when captured, eager otherwise."""
+        if self.cfg.world_size > 1:
+            return self.run_segments(getattr(self, "_seg_graphs", None))
         if getattr(self, "_graph", None) is not None:
             self._replay()
         else:
@@ -783,7 +895,9 @@ class PromptedClipStep:
             self.image.copy_(image_host, non_blocking=True)                 # parse_batch_train :384-387
             self.labels.copy_(label_host.to(torch.int32), non_blocking=True)
             self._copy_done.record(cs)
-        if getattr(self, "_graph", None) is not None:
+        if self.cfg.world_size > 1:
+            self.run_segments(getattr(self, "_seg_graphs", None), wait_event=self._copy_done)
+        elif getattr(self, "_graph", None) is not None:
             self._replay(wait_event=self._copy_done)
         else:
             self._step_part(0)

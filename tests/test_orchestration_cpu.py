@@ -137,7 +137,7 @@ def _free_port():
     return p
 
 
-def _sharded_worker(rank, world, port, tokens, B_global, focal, out):
+def _sharded_worker(rank, world, port, tokens, B_global, focal, out, overlapped=False):
     for p in (ROOT, os.path.join(ROOT, "tests")):
         if p not in sys.path:
             sys.path.insert(0, p)
@@ -155,9 +155,12 @@ def _sharded_worker(rank, world, port, tokens, B_global, focal, out):
                                           pg=dist.group.WORLD, focal_alpha=alpha)
         step.image.copy_(image[rank * Bl:(rank + 1) * Bl])
         step.labels.copy_(label[rank * Bl:(rank + 1) * Bl].int())
-        step.forward_backward()
         step.init_optimizer()
-        step.sgd()
+        if overlapped:          # the segment order of the multi-GPU fast path: asynchronous collectives between segments
+            step.train_step()
+        else:
+            step.forward_backward()
+            step.sgd()
         res = {"grad": step.flat_grad.clone(), "losses": step.losses.clone(), "param": step.flat_param.clone(),
                "logits": step.logits.clone(), "t_hat": step.t_hat.clone(), "classes": (step.c0, step.c1)}
         if rank == 0:  # single-process step on the global batch, same process (same torch math)
@@ -176,8 +179,9 @@ def _sharded_worker(rank, world, port, tokens, B_global, focal, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("focal,n_cls", [(False, 10), (True, 10), (False, 9)])
-def test_class_sharded_data_parallel_step_world2_gloo(focal, n_cls):
+@pytest.mark.parametrize("focal,n_cls,overlapped", [(False, 10, False), (True, 10, False), (False, 9, False),
+                                                    (True, 10, True), (False, 9, True)])
+def test_class_sharded_data_parallel_step_world2_gloo(focal, n_cls, overlapped):
     """Images data-parallel, class prompts sharded by class: all-gather of t_hat, reduce-scatter of dL/dt_hat,
     all-reduce of the flat prompt gradient and of the loss terms give the single-device step (same gradients,
     same losses, same parameters after SGD) on every rank."""
@@ -188,7 +192,8 @@ def test_class_sharded_data_parallel_step_world2_gloo(focal, n_cls):
     world, B_global = 2, 4
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_sharded_worker, args=(world, _free_port(), tokens, B_global, focal, out), nprocs=world, join=True)
+    mp.spawn(_sharded_worker, args=(world, _free_port(), tokens, B_global, focal, out, overlapped), nprocs=world,
+             join=True)
     ref = out[0]["ref"]
     assert out[0]["classes"] == (0, 5) and out[1]["classes"] == (5, 10)
     for r in range(world):
@@ -205,7 +210,7 @@ def test_class_sharded_data_parallel_step_world2_gloo(focal, n_cls):
     assert float((out[0]["param"] - out[1]["param"]).abs().max()) == 0.0         # ranks stay bit-identical
 
 
-def _sharded_worker_other(rank, world, port, kind, tokens, B_global, out):
+def _sharded_worker_other(rank, world, port, kind, tokens, B_global, out, overlapped=False):
     for p in (ROOT, os.path.join(ROOT, "tests")):
         if p not in sys.path:
             sys.path.insert(0, p)
@@ -229,9 +234,12 @@ def _sharded_worker_other(rank, world, port, kind, tokens, B_global, out):
         step = build(Bl, world, rank, dist.group.WORLD)
         step.image.copy_(image[rank * Bl:(rank + 1) * Bl])
         step.labels.copy_(label[rank * Bl:(rank + 1) * Bl].int())
-        step.forward_backward()
         step.init_optimizer()
-        step.sgd()
+        if overlapped:
+            step.train_step()
+        else:
+            step.forward_backward()
+            step.sgd()
         res = {"grad": step.flat_grad.clone(), "losses": step.losses.clone(), "param": step.flat_param.clone(),
                "logits": step.logits.clone(), "classes": (step.c0, step.c1)}
         if rank == 0:
@@ -249,8 +257,8 @@ def _sharded_worker_other(rank, world, port, kind, tokens, B_global, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("kind", ["maple", "cocoop"])
-def test_maple_cocoop_sharded_step_world2_gloo(kind):
+@pytest.mark.parametrize("kind,overlapped", [("maple", False), ("cocoop", False), ("maple", True), ("cocoop", True)])
+def test_maple_cocoop_sharded_step_world2_gloo(kind, overlapped):
     """MaPLe: class-sharded text tower + data-parallel images, the coupling-Linear gradients receive contributions
     from both sides before the all-reduce.  CoCoOp: pure batch sharding (every rank runs all classes for its images),
     only the all-reduce of ctx + meta-net gradients.  Both must equal the single-process step."""
@@ -259,7 +267,8 @@ def test_maple_cocoop_sharded_step_world2_gloo(kind):
     world, B_global = 2, 4
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_sharded_worker_other, args=(world, _free_port(), kind, tokens, B_global, out), nprocs=world, join=True)
+    mp.spawn(_sharded_worker_other, args=(world, _free_port(), kind, tokens, B_global, out, overlapped), nprocs=world,
+             join=True)
     ref = out[0]["ref"]
     want = [(0, 10), (0, 10)] if kind == "cocoop" else [(0, 5), (5, 10)]
     assert [out[r]["classes"] for r in range(world)] == want
