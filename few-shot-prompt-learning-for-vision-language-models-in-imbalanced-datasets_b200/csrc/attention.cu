@@ -11,11 +11,6 @@ int attn_fwd_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H
 int attn_bwd_mma(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int n_seq,
                  int L, int H, int causal, cudaStream_t s);
 bool attn_tc_supported(int L);
-bool attn_small_supported(int L);
-int attn_fwd_small(const void* qkv, void* out, float* lse, int act_dtype, int n_seq, int L, int H, int causal,
-                   cudaStream_t s);
-int attn_bwd_small(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int act_dtype,
-                   int grad_dtype, int n_seq, int L, int H, int causal, cudaStream_t s);
 bool attn_small_mma_supported(int L);
 int attn_fwd_small_mma(const void* qkv, void* out, float* lse, int dtype, int n_seq, int L, int H, int causal,
                        cudaStream_t s);
@@ -30,11 +25,10 @@ using namespace psrc;
 
 static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 // bf16 fast mode: tcgen05 for 32 < L <= 256, one-warp mma.sync tiles for L <= 32 (one 16 x 16 score tile up to 16,
-// 2 x 2 tiles up to 32), flash-style mma.sync otherwise; backend 4 (CUDA-core half-warp kernel) stays selectable
+// 2 x 2 tiles up to 32), flash-style mma.sync otherwise
 static int auto_backend(int L) {
   if (attn_tc_supported(L)) return 3;
-  if (attn_small_mma_supported(L)) return 5;
-  return attn_small_supported(L) ? 4 : 2;
+  return attn_small_mma_supported(L) ? 5 : 2;
 }
 
 extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, int n_seq, int L, int H,
@@ -55,12 +49,7 @@ extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, 
                    "psrc_attn_fwd: mma.sync tile backend needs aligned bf16 and L <= 32 (L=%d)", L);
     return attn_fwd_small_mma(qkv, out, lse, dtype, n_seq, L, H, causal, as_stream(stream));
   }
-  if (backend == 4) {
-    PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out) && attn_small_supported(L),
-                   "psrc_attn_fwd: short-sequence backend needs aligned bf16 and L <= 32 (L=%d)", L);
-    return attn_fwd_small(qkv, out, lse, dtype, n_seq, L, H, causal, as_stream(stream));
-  }
-  PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_fwd: n_seq=%d exceeds the grid limit 65535 of this backend", n_seq);
+  PSRC_CHECK_ARG(backend != 4, "psrc_attn_fwd: backend 4 (CUDA-core short-sequence kernel) was removed; use 5");
   if (backend == 2 || backend == 3) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && al16(qkv) && al16(out), "psrc_attn_fwd: tensor-core backend needs aligned bf16");
     if (backend == 3) {
@@ -91,12 +80,7 @@ extern "C" int psrc_attn_bwd(const void* qkv, const void* out, const void* dout,
                    "psrc_attn_bwd: mma.sync tile backend needs aligned bf16 and L <= 32 (L=%d)", L);
     return attn_bwd_small_mma(qkv, dout, lse, dqkv, dtype, n_seq, L, H, causal, as_stream(stream));
   }
-  if (backend == 4) {
-    PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16 && attn_small_supported(L),
-                   "psrc_attn_bwd: short-sequence backend needs aligned bf16 and L <= 32 (L=%d)", L);
-    return attn_bwd_small(qkv, out, dout, lse, dqkv, dtype, dtype, n_seq, L, H, causal, as_stream(stream));
-  }
-  PSRC_CHECK_ARG(n_seq <= 65535, "psrc_attn_bwd: n_seq=%d exceeds the grid limit 65535 of this backend", n_seq);
+  PSRC_CHECK_ARG(backend != 4, "psrc_attn_bwd: backend 4 (CUDA-core short-sequence kernel) was removed; use 5");
   if (backend == 2 || backend == 3) {
     PSRC_CHECK_ARG(dtype == PSRC_BF16 && ok16, "psrc_attn_bwd: tensor-core backend needs aligned bf16");
     if (backend == 3) {

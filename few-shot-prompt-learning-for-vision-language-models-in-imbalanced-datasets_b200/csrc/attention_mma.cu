@@ -78,7 +78,7 @@ attn_fwd_mma_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __rest
   const int Lp = (L + 15) & ~15;
   uint8_t* Ks = smem_attn;
   uint8_t* Vs = smem_attn + (size_t)Lp * 128;
-  const int h = blockIdx.x, seq = blockIdx.y;
+  const int h = blockIdx.x % H, seq = blockIdx.x / H;   // linear grid: no 65 535 limit on sequences
   const int D = H * 64;
   const long long ld = 3LL * D;
   const __nv_bfloat16* base = qkv + (long long)seq * L * ld + h * 64;
@@ -212,7 +212,7 @@ attn_bwd_mma_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* 
   uint8_t* dOs = Vs + (size_t)Lp * 128;
   float* lse2_s = reinterpret_cast<float*>(dOs + (size_t)Lp * 128);  // lse * log2(e)
   float* delta_s = lse2_s + Lp;
-  const int h = blockIdx.x, seq = blockIdx.y;
+  const int h = blockIdx.x % H, seq = blockIdx.x / H;   // linear grid: no 65 535 limit on sequences
   const int D = H * 64;
   const long long ld = 3LL * D;
   const __nv_bfloat16* base = qkv + (long long)seq * L * ld + h * 64;
@@ -435,7 +435,7 @@ int attn_fwd_mma(const void* qkv, void* out, float* lse, int n_seq, int L, int H
     set_error("attn_fwd (tensor-core): L=%d too long for shared memory", L);
     return PSRC_ERR_UNSUPPORTED;
   }
-  dim3 grid(H, n_seq);
+  dim3 grid((unsigned)H * (unsigned)n_seq);
   const float scale_log2 = 0.125f * kLog2e;
   const __nv_bfloat16* q = reinterpret_cast<const __nv_bfloat16*>(qkv);
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
@@ -459,7 +459,7 @@ int attn_bwd_mma(const void* qkv, const void* out, const void* dout, const float
     set_error("attn_bwd (tensor-core): L=%d too long for shared memory", L);
     return PSRC_ERR_UNSUPPORTED;
   }
-  dim3 grid(H, n_seq);
+  dim3 grid((unsigned)H * (unsigned)n_seq);
   const float scale = 0.125f, scale_log2 = 0.125f * kLog2e;
   const __nv_bfloat16* q = reinterpret_cast<const __nv_bfloat16*>(qkv);
   const __nv_bfloat16* o = reinterpret_cast<const __nv_bfloat16*>(out);

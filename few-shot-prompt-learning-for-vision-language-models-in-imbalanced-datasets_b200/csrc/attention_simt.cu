@@ -35,7 +35,7 @@ attn_fwd_simt_kernel(const T* __restrict__ qkv, T* __restrict__ out, float* __re
   extern __shared__ float sm[];
   float* Ks = sm;
   float* Vs = sm + (size_t)L * kHD;
-  const int h = blockIdx.x, seq = blockIdx.y;
+  const int h = blockIdx.x % H, seq = blockIdx.x / H;   // linear grid: no 65 535 limit on sequences
   const int D = H * kHD, ld = 3 * D;
   const T* base = qkv + (long long)seq * L * ld + h * kHD;
   for (int idx = threadIdx.x; idx < L * kHD; idx += blockDim.x) {
@@ -85,7 +85,7 @@ attn_bwd_simt_kernel(const T* __restrict__ qkv, const T* __restrict__ out, const
   float* bufB = sm + (size_t)L * kHD;        // V, then dO
   float* lse_s = sm + (size_t)2 * L * kHD;
   float* delta_s = lse_s + L;
-  const int h = blockIdx.x, seq = blockIdx.y;
+  const int h = blockIdx.x % H, seq = blockIdx.x / H;   // linear grid: no 65 535 limit on sequences
   const int D = H * kHD, ld = 3 * D;
   const T* base = qkv + (long long)seq * L * ld + h * kHD;
   const T* obase = out + (long long)seq * L * D + h * kHD;
@@ -187,7 +187,7 @@ int attn_fwd_simt(const void* qkv, void* out, float* lse, int dtype, int n_seq, 
     set_error("attn_fwd (CUDA-core): L=%d too long for shared memory", L);
     return PSRC_ERR_UNSUPPORTED;
   }
-  dim3 grid(H, n_seq);
+  dim3 grid((unsigned)H * (unsigned)n_seq);
   const float scale = 0.125f;  // 1/sqrt(64)
   int rc;
   if (dtype == PSRC_BF16) {
@@ -210,7 +210,7 @@ int attn_bwd_simt(const void* qkv, const void* out, const void* dout, const floa
     set_error("attn_bwd (CUDA-core): L=%d too long for shared memory", L);
     return PSRC_ERR_UNSUPPORTED;
   }
-  dim3 grid(H, n_seq);
+  dim3 grid((unsigned)H * (unsigned)n_seq);
   const float scale = 0.125f;
   int rc;
   if (dtype == PSRC_BF16) {

@@ -102,7 +102,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* 
   uint64_t *bar_load = bars, *bar_s = bars + 1, *bar_p = bars + 2, *bar_o = bars + 3, *bar_e = bars + 4;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 5);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int h = blockIdx.x, seq = blockIdx.y;
+  const int h = blockIdx.x % H, seq = blockIdx.x / H;   // linear grid: no 65 535 limit on sequences
   const int D = H * 64;
 
   if (warp == 4) {
@@ -444,7 +444,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
   uint64_t *bar_load = bars, *bar_s = bars + 1, *bar_p = bars + 2, *bar_o = bars + 3, *bar_e = bars + 4;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 5);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int h = blockIdx.x, seq = blockIdx.y;
+  const int h = blockIdx.x % H, seq = blockIdx.x / H;   // linear grid: no 65 535 limit on sequences
   const int D = H * 64;
   const long long ld3 = 3LL * D;
 
@@ -623,7 +623,7 @@ constexpr uint32_t kP3Buf = 128, kP3DP = 64, kP3Out = 256, kP3OutB = 64;
 constexpr int kBwd3Threads = 320;   // warps 0-7 elementwise + epilogue, warp 8: TMEM / TMA / MMA issuer A, warp 9: MMA issuer B
 #ifdef PSRC_ATTN_TIMELINE   // dev instrumentation (tests/attn_timeline.cu): clock64 stamps of one (sequence, head)
 __device__ long long g_tl[2][64];
-#define TL(who, idx) do { if (blockIdx.y == gridDim.y / 2 && blockIdx.x == 3) g_tl[who][idx] = clock64(); } while (0)
+#define TL(who, idx) do { if (blockIdx.x == gridDim.x / 2 + 3) g_tl[who][idx] = clock64(); } while (0)
 #else
 #define TL(who, idx) do { } while (0)
 #endif
@@ -653,7 +653,7 @@ attn_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_c
   uint64_t *bar_load = bars, *bar_s = bars + 1, *bar_p = bars + 3, *bar_o = bars + 5, *bar_e = bars + 7;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 9);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int h = blockIdx.x, seq = blockIdx.y;
+  const int h = blockIdx.x % H, seq = blockIdx.x / H;   // linear grid: no 65 535 limit on sequences
   const int D = H * 64;
   const long long ld3 = 3LL * D;
 
@@ -923,7 +923,7 @@ int attn_fwd_tc(const void* qkv, void* out, float* lse, int n_seq, int L, int H,
   CUtensorMap map;
   int rc = make_map3(&map, qkv, n_seq, L, 3LL * H * 64);
   if (rc) return rc;
-  dim3 grid(H, n_seq);
+  dim3 grid((unsigned)H * (unsigned)n_seq);
   const float scale_log2 = 0.125f * kLog2e;
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
   if (causal) {
@@ -955,7 +955,7 @@ int attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float*
   // when there are two lane tiles (16 steps to pipeline), serial kernel otherwise
   if (version == 3 || (version == 0 && n_mt >= 2)) {
     const size_t smem3 = (size_t)4 * n_mt * kTile + 2 * 256 * sizeof(float) + 128 + 1024;
-    dim3 grid3(H, n_seq);
+    dim3 grid3((unsigned)H * (unsigned)n_seq);
     if (causal) {
       if ((rc = set_smem(attn_bwd_tc3_kernel<true>, smem3))) return rc;
       attn_bwd_tc3_kernel<true><<<grid3, kBwd3Threads, smem3, s>>>(map_qkv, map_do, o, d, lse, dq, L, H, scale, scale_log2);
@@ -967,7 +967,7 @@ int attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float*
     return PSRC_OK;
   }
   const size_t smem = (size_t)4 * n_mt * kTile + 2 * 256 * sizeof(float) + 64 + 1024;
-  dim3 grid(H, n_seq);
+  dim3 grid((unsigned)H * (unsigned)n_seq);
   if (causal) {
     if ((rc = set_smem(attn_bwd_tc_kernel<true>, smem))) return rc;
     attn_bwd_tc_kernel<true><<<grid, kBwdThreads, smem, s>>>(map_qkv, map_do, o, d, lse, dq, L, H, scale, scale_log2);

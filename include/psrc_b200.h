@@ -110,9 +110,9 @@ int psrc_layernorm_bwd(const void* dy, int dy_dtype, const float* x,
  * qkv [n_seq*L, 3*D] with column blocks [q | k | v], head h at h*64 inside each.
  * out [n_seq*L, D]; lse fp32 [n_seq, H, L] (log-sum-exp of the scaled scores).
  * backend: 0 auto, 1 CUDA-core (any dtype), 2 mma.sync tensor-core (bf16), 3 tcgen05/TMEM (bf16, 32 < L <= 256),
- * 4 short-sequence CUDA-core kernel (bf16, L <= 32, one problem per half warp),
- * 5 mma.sync tile kernel (bf16, L <= 32: the truncated text tower, one problem per warp; one 16x16 score tile up
- *   to L = 16, 2 x 2 tiles up to 32). */
+ * 5 mma.sync tile kernel (bf16 or fp16, L <= 32: the truncated text tower, one problem per warp; one 16x16 score
+ *   tile up to L = 16, 2 x 2 tiles up to 32).  (4 was a CUDA-core short-sequence kernel, superseded by 5.)
+ * dtype F16 ("fp16 forward operands"): qkv / out are IEEE half, in the backward dout / dqkv stay bf16; backend 5 only. */
 int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype,
                   int n_seq, int L, int H, int causal, int backend,
                   psrc_stream_t stream);

@@ -37,8 +37,8 @@ def run(n_seq, L, H, causal, backend, reps=10):
 if __name__ == "__main__":
     for (n, L, H, c) in ((128, 201, 12, False), (128, 197, 12, False), (1000, 77, 8, True), (1000, 11, 8, True), (1000, 16, 8, True), (1000, 24, 8, True)):
         row = f"n={n} L={L} H={H} causal={int(c)}"
-        for name, b in (("tcgen05", 3), ("mma.sync", 2), ("short-seq", 4), ("one-tile mma", 5)):
-            if (b == 3 and not (32 < L <= 256)) or (b == 4 and L > 32) or (b == 5 and L > 32):
+        for name, b in (("tcgen05", 3), ("mma.sync", 2), ("one-tile mma", 5)):
+            if (b == 3 and not (32 < L <= 256)) or (b == 5 and L > 32):
                 continue
             f, bw = run(n, L, H, c, b)
             fl = 4.0 * n * H * L * L * 64 * (0.5 if c else 1.0)

@@ -220,19 +220,16 @@ def _attn_ref(qkv, n_seq, L, H, causal):
 def check_attention(res: Results, backend_name: str):
     from psrc_b200 import ops
     dev = "cuda"
-    backend = {"simt": 1, "mma": 2, "tc": 3, "small": 4, "small_mma": 5}[backend_name]
+    backend = {"simt": 1, "mma": 2, "tc": 3, "small_mma": 5}[backend_name]
     g = torch.Generator(device=dev).manual_seed(3)
     cases = [(3, 201, 12, False), (5, 77, 8, True), (7, 16, 8, True), (2, 197, 12, False), (4, 9, 2, True),
              (2, 64, 2, False), (1, 259, 4, False)]
-    dts = [torch.bfloat16] if backend_name in ("mma", "tc", "small", "small_mma") else [torch.float32, torch.bfloat16]
+    dts = [torch.bfloat16] if backend_name in ("mma", "tc", "small_mma") else [torch.float32, torch.bfloat16]
     if backend_name == "small_mma":  # one 16 x 16 score tile per warp: L <= 16
         cases = [(7, 16, 8, True), (4, 9, 2, True), (5, 11, 8, True), (250, 11, 8, True), (2, 1, 2, True),
                  (3, 16, 3, False), (5, 13, 1, False), (1001, 11, 8, True), (3, 8, 2, True),
                  (3, 32, 8, True), (3, 17, 2, False), (5, 25, 1, True), (130, 24, 8, True), (2, 31, 3, False),
                  (4, 20, 12, True)]
-    if backend_name == "small":  # short-sequence kernel: L <= 32 (two problems per warp up to L = 16)
-        cases = [(7, 16, 8, True), (4, 9, 2, True), (5, 11, 8, True), (3, 32, 8, True), (3, 17, 2, False),
-                 (250, 11, 8, True), (2, 1, 2, True), (3, 16, 3, False), (5, 25, 1, True)]
     if backend_name == "tc":  # tcgen05 kernels: 32 < L <= 256
         cases = [(3, 201, 12, False), (5, 77, 8, True), (2, 197, 12, False), (2, 64, 2, False), (3, 128, 2, True),
                  (2, 256, 2, False), (2, 129, 1, True), (37, 201, 12, False),
@@ -593,7 +590,6 @@ GROUPS = {
     "attn_simt": lambda r: check_attention(r, "simt"),
     "attn_mma": lambda r: check_attention(r, "mma"),
     "attn_tc": lambda r: check_attention(r, "tc"),
-    "attn_small": lambda r: check_attention(r, "small"),
     "attn_small_mma": lambda r: check_attention(r, "small_mma"),
     "tokens": check_tokens,
     "loss": check_loss,
