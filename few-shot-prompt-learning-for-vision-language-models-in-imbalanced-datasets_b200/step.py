@@ -699,16 +699,23 @@ class PromptedClipStep:
         lr 0.0025, momentum 0.9, wd 5e-4) over the flat prompt buffer.  lr lives in device memory so a
         captured graph follows the scheduler (`set_lr`)."""
         self.lr_dev = torch.tensor([lr], device=self.device, dtype=torch.float32)
-        self.mom_buf = torch.zeros_like(self.flat_param)   # zero buffer == torch's first-step `buf = g`
+        self.mom_buf = torch.zeros_like(self.flat_param)   # zero buffer == torch's first-step `buf = g` (dampening 0)
         self.sgd_hp = (float(momentum), 0.0, float(weight_decay))
+        self.sgd_nesterov = False
+        self.drop_graphs()
+
+    def drop_graphs(self):
+        """Captured graphs bake the SGD hyper-parameters in as kernel arguments: drop them when those change."""
         self._graph = None
+        self._seg_graphs = None
+        self._text_ahead = False
 
     def set_lr(self, lr: float):
         self.lr_dev.fill_(float(lr))
 
     def sgd(self):
         m, d, wd = self.sgd_hp
-        ops.sgd_step(self.flat_param, self.flat_grad, self.mom_buf, self.lr_dev, m, d, wd, False, False)
+        ops.sgd_step(self.flat_param, self.flat_grad, self.mom_buf, self.lr_dev, m, d, wd, self.sgd_nesterov, False)
 
     def train_step(self):
         """forward + losses + prompt-only backward + SGD on the resident inputs (self.image / self.labels).

@@ -201,15 +201,27 @@ class FlatSGD(torch.optim.Optimizer):
         self._named = list(named_params)                       # [(step key, nn.Parameter)]
         super().__init__([p for _, p in self._named], dict(lr=lr, momentum=momentum, weight_decay=weight_decay,
                                                            dampening=dampening, nesterov=nesterov))
+        if float(dampening) != 0.0:
+            # torch seeds the momentum buffer with the raw first gradient (`buf = g`), which a zero-initialised buffer
+            # reproduces only for dampening 0 -- the value of every prompt-learning yaml (optimizer.py:105-113)
+            raise NotImplementedError("the fused SGD kernel supports OPTIM.SGD_DAMPNING = 0 only")
         step.init_optimizer(lr=lr, momentum=momentum, weight_decay=weight_decay)
-        step.sgd_hp = (float(momentum), float(dampening), float(weight_decay))
-        self._nesterov = bool(nesterov)
+        self._apply_hp(momentum, weight_decay, nesterov)
         self._lr_host = float(lr)
         off = 0
         for k, p in self._named:                               # momentum buffers: views, like torch's state
             n = p.numel()
             self.state[p]["momentum_buffer"] = step.mom_buf[off:off + n].view_as(p)
             off += n
+
+    def _apply_hp(self, momentum, weight_decay, nesterov):
+        """Hyper-parameters of the fused kernel (also the ones baked into captured graphs)."""
+        st = self._step
+        hp, nes = (float(momentum), 0.0, float(weight_decay)), bool(nesterov)
+        if hp != st.sgd_hp or nes != st.sgd_nesterov:
+            st.sgd_hp, st.sgd_nesterov = hp, nes
+            st.drop_graphs()                                   # re-captured on the next fused step
+        self._nesterov = nes
 
     def sync_lr(self):
         lr = float(self.param_groups[0]["lr"])
@@ -246,6 +258,10 @@ class FlatSGD(torch.optim.Optimizer):
         for (k, p), b in zip(self._named, bufs):
             if b is not None:
                 self.state[p]["momentum_buffer"].copy_(b)
+        g0 = self.param_groups[0]
+        if float(g0.get("dampening", 0.0)) != 0.0:
+            raise NotImplementedError("the fused SGD kernel supports dampening 0 only")
+        self._apply_hp(g0["momentum"], g0["weight_decay"], g0.get("nesterov", False))   # resume with other settings
         self._lr_host = None
         self.sync_lr()
 
@@ -383,7 +399,7 @@ class _CustomCLIPBase(nn.Module):
         self._step = PromptedClipStep(scfg, sd, tokens, dev, fixed_embeddings=fixed_embeddings)
         self._infer = None
         self._test_batch = int(_get(cfg, "DATALOADER.TEST.BATCH_SIZE", 100))
-        self._use_graph = bool(_get(cfg, "TRAINER.B200.CUDA_GRAPH", True)) and world == 1 and dev.type == "cuda"
+        self._use_graph = bool(_get(cfg, "TRAINER.B200.CUDA_GRAPH", True)) and dev.type == "cuda"
         self._eager_steps = 0
         emb = sd["token_embedding.weight"][tokens]
         n_ctx = scfg.n_ctx_text
@@ -461,11 +477,19 @@ class _CustomCLIPBase(nn.Module):
         """The trainer's fast path: H2D of the batch, ONE CUDA-graph replay of forward + fused losses +
         prompt-only backward + SGD, and the loss terms left on the device (`.item()` is the caller's sync)."""
         st = self._step
+        w = st.cfg.world_size
+        if w > 1 and image.shape[0] == st.cfg.batch * w:
+            # Dassl's loader has no DistributedSampler: every rank is handed the full BATCH_SIZE (same seed, same
+            # order) -- each rank trains on its contiguous share, as the sharded step expects
+            lo = st.cfg.rank * st.cfg.batch
+            image, label = image[lo:lo + st.cfg.batch], label[lo:lo + st.cfg.batch]
+            next_batch = None
         if image.shape[0] != st.cfg.batch:
             raise RuntimeError(f"training batch {image.shape[0]} != configured per-rank batch {st.cfg.batch} "
                                "(Dassl's train loader drops the last short batch, data_manager.py:42)")
         optim.sync_lr()
-        if self._use_graph and getattr(st, "_graph", None) is None and self._eager_steps >= 1:
+        if self._use_graph and getattr(st, "_graph", None) is None and getattr(st, "_seg_graphs", None) is None \
+                and self._eager_steps >= 1:
             st.capture(warmup=1)
         self._eager_steps += 1
         # any torch-level in-place write to a trainable tensor (load_state_dict on a sub-module, a foreign optimizer,

@@ -284,3 +284,52 @@ def test_maple_cocoop_sharded_step_world2_gloo(kind, overlapped):
         # with exact fp64 accumulation in the restated GEMMs, with or without the last-block pruning): bound = 2^-10
         assert float((o["grad"] - ref["grad"]).abs().max()) < 2.0 ** -10 * float(ref["grad"].abs().max())
     assert float((out[0]["param"] - out[1]["param"]).abs().max()) == 0.0
+
+
+def _trainer_worker(rank, world, port, out):
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        TorchKernels().install(_Patch())
+        import trainer_checks as TC
+        from psrc_b200 import synthetic as S
+        Bg = 4
+        tr, cfg, tokens = TC.make_trainer("PromptSRC", "fp32", device="cpu", **{"DATALOADER.TRAIN_X.BATCH_SIZE": Bg})
+        assert tr.model._step.cfg.world_size == world and tr.model._step.cfg.batch == Bg // world
+        image, label = S.synthetic_batch(Bg, tokens.shape[0], 64, seed=1)
+        losses = []
+        for s_ in range(2):                       # Dassl hands EVERY rank the full batch (no DistributedSampler)
+            tr.batch_idx = 0
+            losses.append(tr.forward_backward({"img": image, "label": label})["loss"])
+        out[rank] = {"losses": losses, "param": tr.model._step.flat_param.clone()}
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_trainer_level_two_ranks_slice_the_full_batch_and_match_one_process(monkeypatch):
+    """`forward_backward(batch)` of the drop-in trainer under torch.distributed -- every rank receives the
+    full BATCH_SIZE from Dassl's loader, trains on its contiguous share through the sharded step, and the two ranks
+    end with the parameters of the single-process trainer on the whole batch."""
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_trainer_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    TorchKernels().install(monkeypatch)
+    import trainer_checks as TC
+    from psrc_b200 import synthetic as S
+    tr, cfg, tokens = TC.make_trainer("PromptSRC", "fp32", device="cpu", **{"DATALOADER.TRAIN_X.BATCH_SIZE": 4})
+    image, label = S.synthetic_batch(4, tokens.shape[0], 64, seed=1)
+    ref_losses = []
+    for s_ in range(2):
+        tr.batch_idx = 0
+        ref_losses.append(tr.forward_backward({"img": image, "label": label})["loss"])
+    ref = tr.model._step.flat_param
+    assert float((out[0]["param"] - out[1]["param"]).abs().max()) == 0.0
+    for r in range(world):
+        assert max(abs(a - b) for a, b in zip(out[r]["losses"], ref_losses)) < 1e-5, (out[r]["losses"], ref_losses)
+        assert float((out[r]["param"] - ref).abs().max()) < 1e-7, float((out[r]["param"] - ref).abs().max())
