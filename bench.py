@@ -376,6 +376,7 @@ def gemm_roofline(torch, ops, dev, shapes, peaks, ms_dev):
     """Every GEMM launch of the step timed alone with CUDA events on the launching stream, operands sized like the
     step's, with the fused epilogue it runs in the step; launch-weighted TFLOP/s against the measured burst peak."""
     tot_f, tot_ms, n_launch, per_shape = 0.0, 0.0, 0, []
+    cublas_f, cublas_ms, ours_ms_same = 0.0, 0.0, 0.0
     for (M, N, K, cnt, mode) in shapes:
         if K % 8 or cnt == 0:
             continue
@@ -410,8 +411,23 @@ def gemm_roofline(torch, ops, dev, shapes, peaks, ms_dev):
         torch.cuda.synchronize()
         t = e0.elapsed_time(e1) / reps
         f = 2.0 * M * N * K
-        per_shape.append({"M": M, "N": N, "K": K, "count": cnt, "epilogue": mode, "us": round(t * 1e3, 2),
-                          "tflops": round(f / (t * 1e-3) / 1e12, 1)})
+        rec = {"M": M, "N": N, "K": K, "count": cnt, "epilogue": mode, "us": round(t * 1e3, 2),
+               "tflops": round(f / (t * 1e-3) / 1e12, 1)}
+        if mode == "none" and M >= 1024:
+            # context, not the product: what the vendor library (cuBLAS through torch.matmul, bf16 in / out, no
+            # epilogue) reaches on the SAME shape on this GPU -- the practical ceiling of a 2-CTA tcgen05 main loop
+            for _ in range(3):
+                torch.matmul(a, w.t(), out=o)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(reps):
+                torch.matmul(a, w.t(), out=o)
+            e1.record()
+            torch.cuda.synchronize()
+            tc = e0.elapsed_time(e1) / reps
+            rec["cublas_us"] = round(tc * 1e3, 2)
+            cublas_f += f * cnt; cublas_ms += tc * cnt; ours_ms_same += t * cnt   # noqa: E702
+        per_shape.append(rec)
         tot_f += f * cnt; tot_ms += t * cnt; n_launch += cnt     # noqa: E702
         del a, w, o, kw
     ach = tot_f / (tot_ms * 1e-3) / 1e12
@@ -420,7 +436,14 @@ def gemm_roofline(torch, ops, dev, shapes, peaks, ms_dev):
             "frac": round(ach / peaks["tf_burst"], 4),
             "peak_source": peaks["source"] + ", burst bf16 (kernel timed alone)", "traffic": gemm_traffic(),
             "launches_per_step": n_launch, "avg_launch_us": round(tot_ms / n_launch * 1e3, 2),
-            "gemm_share_of_step": round(tot_ms / ms_dev, 3), "per_shape": per_shape}
+            "gemm_share_of_step": round(tot_ms / ms_dev, 3),
+            "cublas_same_shapes": None if cublas_ms == 0 else {
+                "what": "plain-epilogue launches of the step (bias, 16-bit out; M >= 1024): this kernel vs torch.matmul "
+                        "(cuBLAS) on the same shapes, launch-weighted",
+                "cublas_tflops": round(cublas_f / (cublas_ms * 1e-3) / 1e12, 1),
+                "this_kernel_tflops": round(cublas_f / (ours_ms_same * 1e-3) / 1e12, 1),
+                "time_ratio_cublas_over_this": round(cublas_ms / ours_ms_same, 3)},
+            "per_shape": per_shape}
 
 
 def b200_arm(args):
