@@ -29,10 +29,9 @@ CASES = {"tiny_promptsrc": ("tiny", 3), "cfg1_promptsrc": ("ViT-B/16", 9),
 # The north star's gradient gate (cosine >= 0.999) is applied to EVERY trainable tensor and to the concatenated vector.
 TOL = {"fp32": dict(logits=1e-4, loss=1e-5, feat=2e-5, cos=0.9999, cos_all=0.9999),
        "bf16": dict(logits=2e-2, loss=1e-2, feat=5e-3, cos=0.999, cos_all=0.999)}
-# The 'tiny' architecture (width 128, embed 64; not a BASELINE config) averages bf16 rounding noise over 8x fewer
-# embedding dimensions, so its bf16-mode logits (14.3 x cosine) carry ~sqrt(8) x the noise: widened bf16 tolerance
-# for that case only.  Its fp32-mode tolerance is the BASELINE one.
-TOL_TINY_BF16 = dict(logits=5e-2, loss=1e-2, feat=8e-3, cos=0.995, cos_all=0.995)
+# (Round 1 widened the 16-bit tolerances for the 64-dim 'tiny' architecture; with fp16 forward operands it meets the
+# BASELINE numbers like every other case -- measured logits <= 4.2e-3, worst gradient cosine 0.99925 -- so it no
+# longer has tolerances of its own.)
 
 
 def run_promptsrc_case(name: str, prec: str, sgd: bool = True) -> dict:
@@ -310,7 +309,7 @@ def run_maple_vitl_case(name: str, prec: str) -> dict:
 
 
 def check_generic(m: dict, prec: str, name: str = "") -> list[str]:
-    t = TOL_TINY_BF16 if (prec == "bf16" and name.startswith("tiny")) else TOL[prec]
+    t = TOL[prec]
     bad = []
     if m["logits_maxabs"] > t["logits"]:
         bad.append(f"logits max|d| {m['logits_maxabs']:.3e} > {t['logits']}")
@@ -342,7 +341,7 @@ OTHER_CASES = {"vitb_maple_ce": run_maple_case, "vitb_maple_focal": run_maple_ca
 
 
 def check(m: dict, prec: str, name: str = "") -> list[str]:
-    t = TOL_TINY_BF16 if (prec == "bf16" and name.startswith("tiny")) else TOL[prec]
+    t = TOL[prec]
     bad = []
     if m["logits_maxabs"] > t["logits"]:
         bad.append(f"logits max|d| {m['logits_maxabs']:.3e} > {t['logits']}")
