@@ -34,7 +34,7 @@ TOL = {"fp32": dict(logits=1e-4, loss=1e-5, feat=2e-5, cos=0.9999, cos_all=0.999
 # longer has tolerances of its own.)
 
 
-def run_promptsrc_case(name: str, prec: str, sgd: bool = True) -> dict:
+def run_promptsrc_case(name: str, prec: str, sgd: bool = True, truncate: bool = True) -> dict:
     from psrc_b200 import ops
     arch_name, depth = CASES[name]
     fx = load_golden(name)
@@ -42,7 +42,8 @@ def run_promptsrc_case(name: str, prec: str, sgd: bool = True) -> dict:
     from psrc_b200 import synthetic as S
     B = fx["label"].shape[0]
     alpha = S.focal_alpha(fx["shots"].tolist(), fx["tokens"].shape[0]) if int(fx.get("focal", 0)) else None
-    step, sd, fixed = promptsrc_setup(arch_name, depth, fx["tokens"], dev, prec, batch=B, focal_alpha=alpha)
+    step, sd, fixed = promptsrc_setup(arch_name, depth, fx["tokens"], dev, prec, batch=B, focal_alpha=alpha,
+                                      truncate=truncate)
     image, label = S.synthetic_batch(B, fx["tokens"].shape[0], S.ARCHS[arch_name].image_resolution, seed=1)
     assert np.array_equal(label.numpy().astype(np.int32), fx["label"]), "synthetic labels drifted from the fixture"
     step.image.copy_(image)

@@ -26,3 +26,16 @@ def test_maple_cocoop_step_matches_reference(name, prec):
     m = OTHER_CASES[name](name, prec)
     bad = check_generic(m, prec, name)
     assert not bad, "; ".join(bad) + f"\nmetrics: {m}"
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", ["tiny_promptsrc", "cfg1_promptsrc"])
+def test_promptsrc_step_dense_text_positions_matches_reference(name, prec):
+    """All 77 text positions instead of the truncation to max(EOT) + 1 (exact under the causal mask): the
+    text tower then runs the tcgen05 attention kernels (L = 77, causal) and -- in the 16-bit mode -- the mixed layout
+    of engine.TowerDtypes (fp16 GEMM operands, bf16 q/k/v/O).  Same fixture, same gates."""
+    if not torch.cuda.is_available():
+        pytest.fail("CUDA device required: this package has no CPU fallback")
+    m = run_promptsrc_case(name, prec, truncate=False)
+    bad = check(m, prec, name)
+    assert not bad, "; ".join(bad) + f"\nmetrics: {m}"
