@@ -394,7 +394,12 @@ class _CustomCLIPBase(nn.Module):
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized():
             world, rank, pg = dist.get_world_size(), dist.get_rank(), dist.group.WORLD
-        scfg = StepConfig(arch=arch, n_cls=tokens.shape[0], batch=int(cfg.DATALOADER.TRAIN_X.BATCH_SIZE) // world,
+        # Dassl drops the last short batch only when the train set holds at least one full batch
+        # (data_manager.py:37-48): a few-shot set SMALLER than BATCH_SIZE arrives as one short batch every iteration,
+        # and the reference trains on it -- the trainer passes that size in (_PromptTrainer._train_batch_size)
+        global _BATCH_OVERRIDE
+        batch_size, _BATCH_OVERRIDE = (_BATCH_OVERRIDE or int(cfg.DATALOADER.TRAIN_X.BATCH_SIZE)), None
+        scfg = StepConfig(arch=arch, n_cls=tokens.shape[0], batch=batch_size // world,
                           prec=prec, world_size=world, rank=rank, process_group=pg, **step_kwargs)
         self._step = PromptedClipStep(scfg, sd, tokens, dev, fixed_embeddings=fixed_embeddings)
         self._infer = None
@@ -828,6 +833,7 @@ def _load_clip(cfg, trainer_name):
     return mod.load_clip_to_cpu(cfg)
 
 
+_BATCH_OVERRIDE = None      # set by the trainer for the next CustomCLIP it builds (train set smaller than BATCH_SIZE)
 CLIP_MODEL_FACTORY = None   # callable(cfg, trainer_name) -> reference-keyed CLIP module (fp32)
 TOKEN_FACTORY = None        # callable(cfg, classnames) -> int64 [C, 77] tokenised prompts, or None for the reference tokenizer
 
@@ -836,6 +842,12 @@ class _PromptTrainer(TrainerX):
     MODEL_NAME = "prompt_learner"
 
     def _tokens(self, classnames):
+        """Called right before the CustomCLIP is built: also tells `_build` the batch size the loader will deliver."""
+        global _BATCH_OVERRIDE
+        bs = int(self.cfg.DATALOADER.TRAIN_X.BATCH_SIZE)
+        train_x = getattr(getattr(self.dm, "dataset", None), "train_x", None)
+        if train_x is not None and 0 < len(train_x) < bs:
+            _BATCH_OVERRIDE = len(train_x)            # one short batch per epoch, not dropped (data_manager.py:37-48)
         return TOKEN_FACTORY(self.cfg, classnames) if TOKEN_FACTORY is not None else None
 
     def _finish_build(self, registered_module):
@@ -853,6 +865,28 @@ class _PromptTrainer(TrainerX):
     def parse_batch_train(self, batch):
         # no `.to(device)` round trip: the fused step copies the (pinned) host batch straight into its buffers
         return batch["img"], batch["label"]
+
+    def save_model(self, epoch, directory, is_best=False, val_result=None, model_name=""):
+        """Dassl's save_model (trainer.py:118-145) writes the registered module's whole state_dict -- for PromptSRC /
+        MaPLe the complete frozen CLIP (~0.6 GB at ViT-B/16) next to 46 080 trained scalars.  With
+        `TRAINER.B200.SLIM_CHECKPOINT = True` only the trainable tensors are written; the file keeps the
+        reference's layout and key names, and both this package and the reference load it (`load_model` uses
+        strict=False and the frozen weights come from the CLIP checkpoint anyway).  Default False: byte-for-byte the
+        reference's behaviour."""
+        if not bool(_get(self.cfg, "TRAINER.B200.SLIM_CHECKPOINT", False)):
+            return super().save_model(epoch, directory, is_best=is_best, val_result=val_result, model_name=model_name)
+        full = {}
+        for name in self.get_model_names():
+            m = self._models[name]
+            full[name] = m.state_dict
+            keep = {k for k, p_ in m.named_parameters() if p_.requires_grad}
+            m.state_dict = (lambda sd_fn, keep_: (lambda *a, **k: {kk: v for kk, v in sd_fn(*a, **k).items()
+                                                                    if kk in keep_}))(m.state_dict, keep)
+        try:
+            return super().save_model(epoch, directory, is_best=is_best, val_result=val_result, model_name=model_name)
+        finally:
+            for name, fn in full.items():
+                del self._models[name].state_dict          # back to the class's method
 
     def load_model(self, directory, epoch=None):                             # promptsrc.py:390-420
         if not directory:

@@ -164,3 +164,26 @@ def test_lookahead_loader_yields_same_batches_with_the_following_one_attached():
                 assert nxt is None
     assert "_next" not in batches[0]            # the loader's own dicts are not modified
     assert _next_of({"img": 1, "label": 2}) is None
+
+
+def test_train_set_smaller_than_batch_size_builds_the_step_for_the_short_batch(monkeypatch):
+    """Dassl drops the last short batch only when the train set holds a full one (data_manager.py:37-48); a
+    1-shot x 2-class set with BATCH_SIZE 3 arrives as ONE batch of 2 every epoch and the reference trains on it."""
+    fk = FakeKernels()
+    fk.install(monkeypatch)
+    import trainer_checks as TC
+    from psrc_b200 import trainers as T
+    real_dm = TC.FakeDM
+
+    class SmallDM(real_dm):
+        def __init__(self, classnames):
+            super().__init__(classnames)
+            self.dataset.train_x = [object(), object()]          # 2 training items < BATCH_SIZE = 3
+
+    monkeypatch.setattr(TC, "FakeDM", SmallDM)
+    tr, cfg, tokens = TC.make_trainer("PromptSRC", "fp32", device="cpu")
+    assert cfg.DATALOADER.TRAIN_X.BATCH_SIZE == 3 and tr.model._step.cfg.batch == 2
+    assert T._BATCH_OVERRIDE is None                                  # consumed by the build
+    monkeypatch.setattr(TC, "FakeDM", real_dm)
+    tr2, _, _ = TC.make_trainer("PromptSRC", "fp32", device="cpu")
+    assert tr2.model._step.cfg.batch == 3

@@ -34,6 +34,8 @@ def test_eval_logits_cached_text_and_checkpoint_roundtrip():
     m = TC.check_eval_and_checkpoint("fp32")
     assert m["ckpt_restore_maxabs"] == 0.0 and not m["missing_state_keys"], m
     assert m["eval_logits_maxabs"] < 1e-4 and m["eval_argmax_equal"] and m["eval_shape_ok"], m
+    assert len(m["slim_keys"]) == 2 * TC.DEPTH and m["slim_restore_maxabs"] == 0.0 and m["state_dict_method_restored"], m
+    assert m["slim_bytes"] < 4 * m["full_state_numel"] / 20, m        # a small fraction of the full state
 
 
 def test_promptsrc_gpa_three_epochs_matches_reference_aggregation():

@@ -153,6 +153,20 @@ def check_eval_and_checkpoint(prec="fp32"):
         tr.model._step.flat_param.add_(1.0)
         tr.load_model(d, epoch=1)
         m["ckpt_restore_maxabs"] = float((tr.model._step.flat_param - before).abs().max())
+    # slim checkpoint (TRAINER.B200.SLIM_CHECKPOINT): trainable tensors only, still loadable
+    with tempfile.TemporaryDirectory() as d:
+        tr.cfg.TRAINER.B200["SLIM_CHECKPOINT"] = True
+        tr.save_model(0, d)
+        tr.cfg.TRAINER.B200["SLIM_CHECKPOINT"] = False
+        f = os.path.join(d, "VLPromptLearner", "model.pth.tar-1")
+        slim = torch.load(f, weights_only=False)["state_dict"]
+        m["slim_keys"] = sorted(slim)
+        m["slim_bytes"], m["full_state_numel"] = os.path.getsize(f), sum(v.numel() for v in tr.model.state_dict().values())
+        before = tr.model._step.flat_param.clone()
+        tr.model._step.flat_param.mul_(0.5)
+        tr.load_model(d, epoch=1)
+        m["slim_restore_maxabs"] = float((tr.model._step.flat_param - before).abs().max())
+        m["state_dict_method_restored"] = len(tr.model.state_dict()) > len(slim)
     need = {"prompt_learner.ctx", "prompt_learner.token_prefix", "prompt_learner.token_suffix", "image_encoder.VPT",
             "image_encoder.transformer.resblocks.1.VPT_shallow", "text_encoder.transformer.resblocks.2.VPT_shallow",
             "image_encoder.conv1.weight", "text_encoder.text_projection", "logit_scale",
