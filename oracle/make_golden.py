@@ -146,6 +146,9 @@ def run_coop(name, arch_name, classnames, batch, extra):
     image, label = S.synthetic_batch(batch, len(classnames), arch.image_resolution, seed=2)
     tokens = model.tokenized_prompts.clone()
     ctx0 = model.prompt_learner.ctx.detach().clone()
+    model.eval()
+    with torch.no_grad():
+        logits_ref = model(image)                                   # the REFERENCE's logits of the initial prompts
     model.train()
     opt = torch.optim.SGD(model.prompt_learner.parameters(), lr=0.002, momentum=0.9, weight_decay=5e-4)
     loss = model(image, label, None)                                # coop.py:456
@@ -166,9 +169,10 @@ def run_coop(name, arch_name, classnames, batch, extra):
     print(f"[{name}] reference loss={float(loss):.6f}; oracle |d|={abs(float(o['loss']) - float(loss)):.2e} "
           f"grad cos={cos(ctx.grad, grad):.7f} rel={rel(ctx.grad, grad):.2e}")
     assert abs(float(o["loss"]) - float(loss)) < 2e-5 and cos(ctx.grad, grad) > 0.99999
+    assert float((o["logits"].detach() - logits_ref).abs().max()) < 1e-4
     np.savez_compressed(os.path.join(GOLD, name + ".npz"), tokens=tokens.numpy().astype(np.int32),
                         label=label.numpy().astype(np.int32), loss=np.float32(float(loss)), ctx0=ctx0.numpy(),
-                        logits=o["logits"].detach().numpy(), logits_after=logits_after.numpy(),
+                        logits=logits_ref.numpy(), logits_after=logits_after.numpy(),
                         shots=np.array(shots, dtype=np.int32), classnames=np.array(classnames),
                         **{"grad/prompt_learner.ctx": grad.numpy(), "after/prompt_learner.ctx": after.numpy()})
 
@@ -198,6 +202,9 @@ def run_maple(name, arch_name, classnames, batch, depth, extra):
     tokens = model.tokenized_prompts.clone()
     pl = model.prompt_learner
     init = {n: p.detach().clone() for n, p in model.named_parameters() if p.requires_grad}
+    model.eval()
+    with torch.no_grad():
+        logits_ref = model(image)                                   # the REFERENCE's logits of the initial prompts
     model.train()
     opt = torch.optim.SGD([p for p in model.parameters() if p.requires_grad], lr=0.0035, momentum=0.9, weight_decay=5e-4)
     loss = model(image, label)                                      # maple.py:320
@@ -219,8 +226,9 @@ def run_maple(name, arch_name, classnames, batch, depth, extra):
     print(f"[{name}] reference loss={float(loss):.6f}; oracle |d|={abs(float(o['loss']) - float(loss)):.2e} "
           f"worst grad cos={worst:.7f} trainable={sorted(grads)}")
     assert abs(float(o["loss"]) - float(loss)) < 2e-5 and worst > 0.99999
+    assert float((o["logits"].detach() - logits_ref).abs().max()) < 1e-4
     fx = {"tokens": tokens.numpy().astype(np.int32), "label": label.numpy().astype(np.int32),
-          "loss": np.float32(float(loss)), "logits": o["logits"].detach().numpy(),
+          "loss": np.float32(float(loss)), "logits": logits_ref.numpy(),
           "shots": np.array(shots, dtype=np.int32), "n_ctx": np.int32(n_ctx), "depth": np.int32(depth)}
     for n in grads:
         if n.endswith(".weight"):  # [768, 512] coupling matrices: every 8th row keeps the fixture small
@@ -252,6 +260,9 @@ def run_cocoop(name, arch_name, classnames, batch, extra):
     image, label = S.synthetic_batch(batch, len(classnames), arch.image_resolution, seed=4)
     tokens = model.tokenized_prompts.clone()
     init = {n: p.detach().clone() for n, p in model.named_parameters() if p.requires_grad}
+    model.eval()
+    with torch.no_grad():
+        logits_ref = model(image)                                   # the REFERENCE's logits of the initial prompts
     model.train()
     opt = torch.optim.SGD([p for p in model.parameters() if p.requires_grad], lr=0.002, momentum=0.9, weight_decay=5e-4)
     loss = model(image, label)                                      # cocoop.py:323
@@ -270,8 +281,9 @@ def run_cocoop(name, arch_name, classnames, batch, extra):
     print(f"[{name}] reference loss={float(loss):.6f}; oracle |d|={abs(float(o['loss']) - float(loss)):.2e} "
           f"worst grad cos={worst:.7f} trainable={sorted(grads)}")
     assert abs(float(o["loss"]) - float(loss)) < 2e-5 and worst > 0.99999
+    assert float((o["logits"].detach() - logits_ref).abs().max()) < 1e-4
     fx = {"tokens": tokens.numpy().astype(np.int32), "label": label.numpy().astype(np.int32),
-          "loss": np.float32(float(loss)), "logits": o["logits"].detach().numpy(),
+          "loss": np.float32(float(loss)), "logits": logits_ref.numpy(),
           "shots": np.array(shots, dtype=np.int32), "n_ctx": np.int32(n_ctx)}
     for n in grads:
         fx["init/" + n], fx["grad/" + n], fx["after/" + n] = init[n].numpy(), grads[n].numpy(), after[n].numpy()
