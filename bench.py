@@ -68,7 +68,6 @@ def parse_args():
     ap.add_argument("--e2e-breakdown", action="store_true", help="diagnostic timings of the host-facing path (stderr)")
     ap.add_argument("--overlap-zs", type=int, default=1,
                     help="bit 0: frozen tower forward on a second stream (default on); bit 1: text backward on a second stream")
-    ap.add_argument("--graph-multi", action="store_true", help="multi-GPU: capture the step incl. NCCL (experimental)")
     ap.add_argument("--no-truncate", action="store_true", help="run all 77 text positions (dense-equivalent)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-torch-gpu-baseline", action="store_true",
