@@ -850,8 +850,40 @@ class _PromptTrainer(TrainerX):
             _BATCH_OVERRIDE = len(train_x)            # one short batch per epoch, not dropped (data_manager.py:37-48)
         return TOKEN_FACTORY(self.cfg, classnames) if TOKEN_FACTORY is not None else None
 
+    def _init_weights(self, module):
+        """`if cfg.MODEL.INIT_WEIGHTS: load_pretrained_weights(self.model, ...)` of every reference build_model
+        (promptsrc.py:253-254, coop.py:424-426; dassl/utils/torchtools.py:267-311: matching names and sizes are loaded,
+        the rest ignored).  The prompt tensors land in the flat buffer through their nn.Parameter views.  The frozen CLIP
+        tensors were already converted to the kernel layout when the module was built, so a file that would CHANGE one of
+        them is refused instead of being half-applied."""
+        path = _get(self.cfg, "MODEL.INIT_WEIGHTS", "")
+        if not path:
+            return
+        ckpt = torch.load(path, map_location="cpu", weights_only=False)
+        sd = ckpt["state_dict"] if "state_dict" in ckpt else ckpt
+        own = module.state_dict()
+        trainable = {k for k, p_ in module.named_parameters() if p_.requires_grad}
+        take, frozen_changed = {}, []
+        for k, v in sd.items():
+            k = k[7:] if k.startswith("module.") else k
+            if k in own and own[k].size() == v.size():
+                if k in trainable:
+                    take[k] = v
+                elif not torch.equal(own[k].detach().cpu().to(v.dtype), v.cpu()):
+                    frozen_changed.append(k)
+        if frozen_changed:
+            raise NotImplementedError(f"MODEL.INIT_WEIGHTS would overwrite frozen CLIP tensors ({frozen_changed[:3]} ...) "
+                                      "after their conversion to the kernel layout; load them into the CLIP model instead")
+        if not take:
+            import warnings
+            warnings.warn(f"Cannot load {path} (check the key names manually)")
+        module.load_state_dict(take, strict=False)
+        self.model.params_changed()
+        print(f'Successfully loaded pretrained weights from "{path}" ({len(take)} trainable tensors)')
+
     def _finish_build(self, registered_module):
         cfg = self.cfg
+        self._init_weights(self.model)
         self.optim = self.model.make_optimizer(cfg.OPTIM)                    # SGD of optim/optimizer.py:105-113
         self.sched = build_scheduler(self.optim, cfg.OPTIM)
         self.register_model(self.MODEL_NAME, registered_module, self.optim, self.sched)

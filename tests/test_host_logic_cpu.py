@@ -187,3 +187,22 @@ def test_train_set_smaller_than_batch_size_builds_the_step_for_the_short_batch(m
     monkeypatch.setattr(TC, "FakeDM", real_dm)
     tr2, _, _ = TC.make_trainer("PromptSRC", "fp32", device="cpu")
     assert tr2.model._step.cfg.batch == 3
+
+
+def test_init_weights_loads_prompts_and_refuses_changed_frozen_tensors(monkeypatch, tmp_path):
+    """`cfg.MODEL.INIT_WEIGHTS` (promptsrc.py:253-254) is honoured for the prompt tensors; a file that would
+    change a frozen CLIP tensor (already converted to the kernel layout) is refused, not half-applied."""
+    fk = FakeKernels()
+    fk.install(monkeypatch)
+    import trainer_checks as TC
+    tr, cfg, tokens = TC.make_trainer("PromptSRC", "fp32", device="cpu")
+    sd = {k: v.clone() for k, v in tr.model.state_dict().items()}
+    sd["prompt_learner.ctx"] = torch.full_like(sd["prompt_learner.ctx"], 0.25)
+    f = tmp_path / "init.pth.tar"
+    torch.save({"state_dict": sd, "epoch": 3}, f)
+    tr2, _, _ = TC.make_trainer("PromptSRC", "fp32", device="cpu", **{"MODEL": {"INIT_WEIGHTS": str(f)}})
+    assert float(tr2.model._step.params["ctx"].min()) == 0.25 == float(tr2.model._step.params["ctx"].max())
+    sd["image_encoder.ln_pre.weight"] = sd["image_encoder.ln_pre.weight"] + 1.0
+    torch.save({"state_dict": sd}, f)
+    with pytest.raises(NotImplementedError):
+        TC.make_trainer("PromptSRC", "fp32", device="cpu", **{"MODEL": {"INIT_WEIGHTS": str(f)}})
