@@ -526,6 +526,23 @@ def b200_arm(args):
     for _ in range(2):
         step.train_step_host(image_host, label_host, next_host=nxt)
     ms_e2e = timed(lambda: step.train_step_host(image_host, label_host, next_host=nxt), args.steps)
+    # the same call fed by the on-device input pipeline: uint8 256 x 256 canvases + crop geometry from
+    # pinned host memory (a quarter of the fp32 bytes), crop / bicubic resample / flip / normalise kernel, then the step
+    e2e_u8 = None
+    if world == 1 and not conf.get("infer"):
+        gi = torch.Generator().manual_seed(7)
+        Hc = 256
+        item = {"u8": torch.randint(0, 256, (B, Hc, Hc, 3), generator=gi, dtype=torch.uint8).pin_memory(),
+                "geom_f": torch.tensor([[200.0 / arch.image_resolution] * 2 + [0.0, 0.0]] * B).pin_memory(),
+                "geom_i": torch.tensor([[0, 0, 200, 200, k % 2] for k in range(B)], dtype=torch.int32).pin_memory()}
+        for _ in range(2):
+            step.train_step_host_u8(item, label_host, next_host=(item, label_host))
+        ms_u8 = timed(lambda: step.train_step_host_u8(item, label_host, next_host=(item, label_host)), args.steps)
+        e2e_u8 = {"value": B * world / (ms_u8 * 1e-3), "unit": UNIT, "ms_per_step": ms_u8,
+                  "h2d_bytes_per_step": step._pre.bytes_per_batch(), "d2h_bytes_per_step": 16,
+                  "api": "PromptedClipStep.train_step_host_u8 (uint8 canvases + crop boxes in, device resample)"}
+        step.image.copy_(image_host)               # the fp32-fed legs below keep their inputs
+        step.labels.copy_(label_host.to(torch.int32))
     if args.e2e_breakdown and rank == 0 and world == 1:    # diagnostic: where does e2e - value go on this box?
         again = timed(step.run, args.steps)
         step.stage_host(*nxt)
@@ -621,6 +638,7 @@ def b200_arm(args):
                 "e2e": {"value": gb / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                         "h2d_bytes_per_step": image_host.numel() * 4 + label_host.numel() * 8,
                         "d2h_bytes_per_step": 16, "api": "PromptedClipStep.train_step_host (pinned host batch; the following batch's H2D is issued under the step)"},
+                "e2e_u8_input_pipeline": e2e_u8,
                 "gpu_launches": launches * args.steps, "gpu_launches_per_step": launches,
                 "cuda_graph": use_graph, "clocks": clocks, "loss": loss_value,
                 "step_tflops_per_gpu": round(tf_step, 1),
