@@ -883,7 +883,7 @@ class _PromptTrainer(TrainerX):
 
     def _finish_build(self, registered_module):
         cfg = self.cfg
-        self._init_weights(self.model)
+        self._init_weights(registered_module)          # the module the reference passes (coop.py:424-426: prompt_learner)
         self.optim = self.model.make_optimizer(cfg.OPTIM)                    # SGD of optim/optimizer.py:105-113
         self.sched = build_scheduler(self.optim, cfg.OPTIM)
         self.register_model(self.MODEL_NAME, registered_module, self.optim, self.sched)
