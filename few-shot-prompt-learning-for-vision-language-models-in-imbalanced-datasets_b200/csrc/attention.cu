@@ -33,8 +33,9 @@ static int auto_backend(int L) {
 
 extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, int n_seq, int L, int H,
                              int causal, int backend, psrc_stream_t stream) {
-  PSRC_CHECK_ARG(qkv && out && lse, "psrc_attn_fwd: null pointer");
   PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && H > 0, "psrc_attn_fwd: bad shape n_seq=%d L=%d H=%d", n_seq, L, H);
+  if (n_seq == 0) return PSRC_OK;   // (empty tensors have NULL storage)
+  PSRC_CHECK_ARG(qkv && out && lse, "psrc_attn_fwd: null pointer");
   PSRC_CHECK_ARG(dtype >= PSRC_F32 && dtype <= PSRC_F16, "psrc_attn_fwd: bad dtype");
   if (n_seq == 0) return PSRC_OK;
   if (dtype == PSRC_F16) {   // fp16 forward operands: the short-sequence tile kernels only (the truncated text tower)
@@ -63,8 +64,9 @@ extern "C" int psrc_attn_fwd(const void* qkv, void* out, float* lse, int dtype, 
 
 extern "C" int psrc_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
                              int dtype, int n_seq, int L, int H, int causal, int backend, psrc_stream_t stream) {
-  PSRC_CHECK_ARG(qkv && out && dout && lse && dqkv, "psrc_attn_bwd: null pointer");
   PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && H > 0, "psrc_attn_bwd: bad shape n_seq=%d L=%d H=%d", n_seq, L, H);
+  if (n_seq == 0) return PSRC_OK;
+  PSRC_CHECK_ARG(qkv && out && dout && lse && dqkv, "psrc_attn_bwd: null pointer");
   PSRC_CHECK_ARG(dtype >= PSRC_F32 && dtype <= PSRC_F16, "psrc_attn_bwd: bad dtype");
   if (n_seq == 0) return PSRC_OK;
   const bool ok16 = al16(qkv) && al16(out) && al16(dout) && al16(dqkv);

@@ -350,6 +350,7 @@ static bool al16r(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) 
 
 extern "C" int psrc_attn_row_fwd(const void* qkv, void* out, float* lse, int dtype, const int32_t* idx, int n_seq,
                                  int L, int H, int causal, psrc_stream_t stream) {
+  if (n_seq == 0) return PSRC_OK;   // (empty tensors have NULL storage)
   PSRC_CHECK_ARG(qkv && out && lse, "psrc_attn_row_fwd: null pointer");
   PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && L <= 32 * arow::kMaxKeysPerLane && H > 0,
                  "psrc_attn_row_fwd: bad shape n_seq=%d L=%d H=%d (L <= %d)", n_seq, L, H, 32 * arow::kMaxKeysPerLane);
@@ -374,6 +375,7 @@ extern "C" int psrc_attn_row_fwd(const void* qkv, void* out, float* lse, int dty
 extern "C" int psrc_attn_row_bwd(const void* qkv, const void* dout, const float* lse, void* dqkv, int dtype,
                                  int grad_dtype, const int32_t* idx, int n_seq, int L, int H, int causal,
                                  psrc_stream_t stream) {
+  if (n_seq == 0) return PSRC_OK;
   PSRC_CHECK_ARG(qkv && dout && lse && dqkv, "psrc_attn_row_bwd: null pointer");
   PSRC_CHECK_ARG(n_seq >= 0 && L > 0 && L <= 32 * arow::kMaxKeysPerLane && H > 0,
                  "psrc_attn_row_bwd: bad shape n_seq=%d L=%d H=%d (L <= %d)", n_seq, L, H, 32 * arow::kMaxKeysPerLane);

@@ -168,6 +168,7 @@ extern "C" int psrc_gemm(const psrc_gemm_args* args, psrc_stream_t stream) {
   PSRC_CHECK_ARG(args != nullptr, "psrc_gemm: null args");
   const psrc_gemm_args& a = *args;
   PSRC_CHECK_ARG(a.M >= 0 && a.N > 0 && a.K > 0, "psrc_gemm: bad shape M=%d N=%d K=%d", a.M, a.N, a.K);
+  if (a.M == 0) return PSRC_OK;   // an empty operand has no storage (NULL): nothing to do, not an error
   PSRC_CHECK_ARG(a.A && a.W && a.out, "psrc_gemm: null A/W/out");
   PSRC_CHECK_ARG(a.ab_dtype >= PSRC_F32 && a.ab_dtype <= PSRC_F16, "psrc_gemm: bad ab_dtype %d", a.ab_dtype);
   PSRC_CHECK_ARG(a.out_dtype >= PSRC_F32 && a.out_dtype <= PSRC_F16, "psrc_gemm: bad out_dtype");

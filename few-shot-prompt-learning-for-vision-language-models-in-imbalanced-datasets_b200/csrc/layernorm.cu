@@ -253,8 +253,8 @@ extern "C" int psrc_layernorm_fwd(const float* x, const float* gamma, const floa
                                   int out_dtype, float* mean, float* rstd, int rows, int D, float eps,
                                   psrc_stream_t stream) {
   CHECK_LN_COMMON("psrc_layernorm_fwd");
+  if (rows == 0) return PSRC_OK;   // (empty tensors have NULL storage)
   PSRC_CHECK_ARG(x && gamma && beta && y, "psrc_layernorm_fwd: null pointer");
-  if (rows == 0) return PSRC_OK;
   if (out_dtype == PSRC_F16)
     return launch_fwd<__half>(x, nullptr, 0, gamma, beta, y, mean, rstd, rows, D, eps, as_stream(stream));
   if (out_dtype == PSRC_BF16)
@@ -266,8 +266,8 @@ extern "C" int psrc_layernorm_bwd(const void* dy, int dy_dtype, const float* x, 
                                   const float* mean, const float* rstd, const float* dx_in, float* dx_out,
                                   void* dx_act, int act_dtype, int rows, int D, psrc_stream_t stream) {
   CHECK_LN_COMMON("psrc_layernorm_bwd");
-  PSRC_CHECK_ARG(dy && x && gamma && mean && rstd && dx_out, "psrc_layernorm_bwd: null pointer");
   if (rows == 0) return PSRC_OK;
+  PSRC_CHECK_ARG(dy && x && gamma && mean && rstd && dx_out, "psrc_layernorm_bwd: null pointer");
   return bwd_dispatch(dy, dy_dtype, x, nullptr, 0, gamma, mean, rstd, dx_in, dx_out, dx_act, act_dtype, rows, D,
                       as_stream(stream));
 }
@@ -277,8 +277,8 @@ extern "C" int psrc_gather_ln_fwd(const float* x, const int32_t* idx, const floa
                                   float eps, psrc_stream_t stream) {
   const int rows = n_seq;
   CHECK_LN_COMMON("psrc_gather_ln_fwd");
-  PSRC_CHECK_ARG(x && gamma && beta && y && L > 0, "psrc_gather_ln_fwd: bad arguments");
   if (rows == 0) return PSRC_OK;
+  PSRC_CHECK_ARG(x && gamma && beta && y && L > 0, "psrc_gather_ln_fwd: bad arguments");
   if (out_dtype == PSRC_F16)
     return launch_fwd<__half>(x, idx, L, gamma, beta, y, mean, rstd, rows, D, eps, as_stream(stream));
   if (out_dtype == PSRC_BF16)
@@ -292,8 +292,8 @@ extern "C" int psrc_gather_ln_bwd(const void* dy, int dy_dtype, const float* x, 
                                   int D, psrc_stream_t stream) {
   const int rows = n_seq * L;
   CHECK_LN_COMMON("psrc_gather_ln_bwd");
-  PSRC_CHECK_ARG(dy && x && gamma && mean && rstd && dx && L > 0, "psrc_gather_ln_bwd: bad arguments");
   if (rows == 0) return PSRC_OK;
+  PSRC_CHECK_ARG(dy && x && gamma && mean && rstd && dx && L > 0, "psrc_gather_ln_bwd: bad arguments");
   return bwd_dispatch(dy, dy_dtype, x, idx, L, gamma, mean, rstd, dx_in, dx, dx_act, act_dtype, rows, D,
                       as_stream(stream));
 }
