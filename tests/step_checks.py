@@ -409,3 +409,38 @@ if __name__ == "__main__":
                 print(f"   {k:32s} {v}")
             rc |= bool(bad)
     sys.exit(rc)
+
+
+def run_tiny_oracle_case(B: int, name_lens: list, prec: str) -> dict:
+    """PromptSRC on the tiny architecture at arbitrary (small) batch / class counts against the oracle restatement run
+    on the CPU in this process (edge cases: one image, two classes, one long class name)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import clip_oracle as O
+    from psrc_b200 import synthetic as S
+    arch = S.ARCHS["tiny"]
+    depth, n_ctx = 3, 4
+    tokens = S.synthetic_tokens(len(name_lens), name_lens=name_lens)
+    sd = S.make_clip_state_dict(arch, seed=0)
+    image, label = S.synthetic_batch(B, tokens.shape[0], arch.image_resolution, seed=1)
+    tk = torch.as_tensor(tokens)
+    fixed = O.teacher_text_features(sd, tk, arch.transformer_heads)
+    deep = S.make_deep_prompts(arch, n_ctx, n_ctx, depth, depth, seed=100)
+    ctx = sd["token_embedding.weight"][tk[0, 1:1 + n_ctx]].clone().requires_grad_(True)
+    vpt = deep["visual.VPT"].clone().requires_grad_(True)
+    dv = {i: deep[f"visual.transformer.resblocks.{i}.VPT_shallow"].clone().requires_grad_(True) for i in range(1, depth)}
+    dtx = {i: deep[f"transformer.resblocks.{i}.VPT_shallow"].clone().requires_grad_(True) for i in range(1, depth)}
+    o = O.promptsrc_step(sd, tk, image, label, ctx, vpt, dv, dtx, fixed, n_ctx, arch.vision_heads, arch.transformer_heads)
+    o["loss"].backward()
+    og = {"ctx": ctx.grad, "vpt": vpt.grad}
+    og.update({f"vision.{i}": t.grad for i, t in dv.items()})
+    og.update({f"text.{i}": t.grad for i, t in dtx.items()})
+    step, _, _ = promptsrc_setup("tiny", depth, tokens, "cuda", prec, batch=B, sd=sd)
+    step.image.copy_(image)
+    step.labels.copy_(label.int())
+    step.forward_backward()
+    torch.cuda.synchronize()
+    cs = {k: cos(step.grads[k], og[k]) for k in step.params}
+    return {"logits_maxabs": float((step.logits.cpu() - o["logits"].detach()).abs().max()),
+            "loss_rel": abs(float(step.losses.sum()) - float(o["loss"].detach())) / abs(float(o["loss"].detach())),
+            "gradcos_worst": min(cs.values()), "gradcos_worst_key": min(cs, key=cs.get),
+            "argmax_equal": bool((step.logits.argmax(1).cpu() == o["logits"].argmax(1)).all()), "Lt": step.Lt}

@@ -39,3 +39,19 @@ def test_promptsrc_step_dense_text_positions_matches_reference(name, prec):
     m = run_promptsrc_case(name, prec, truncate=False)
     bad = check(m, prec, name)
     assert not bad, "; ".join(bad) + f"\nmetrics: {m}"
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("B,name_lens", [(1, [1, 2]), (2, [30]), (1, [1, 1, 1, 1, 1, 1, 1])])
+def test_promptsrc_step_edge_sizes_match_oracle(B, name_lens, prec):
+    """One image; two classes / ONE class (softmax over a single logit: CE = 0, KL = 0) / a 30-token class name (text
+    length 37: the tcgen05 causal attention instead of the short-sequence kernels); seven classes for one image."""
+    from step_checks import TOL, run_tiny_oracle_case
+    if not torch.cuda.is_available():
+        pytest.fail("CUDA device required: this package has no CPU fallback")
+    m = run_tiny_oracle_case(B, name_lens, prec)
+    t = TOL[prec]
+    assert m["logits_maxabs"] <= t["logits"] and m["loss_rel"] <= t["loss"], m
+    assert m["gradcos_worst"] >= t["cos"], m
+    if prec == "fp32":
+        assert m["argmax_equal"], m
