@@ -222,10 +222,11 @@ class PromptedClipStep:
         self.focal_alpha = torch.tensor(cfg.focal_alpha, device=dev, dtype=torch.float32) \
             if cfg.focal_alpha is not None else None
         if need_vb:
-            self.vpt_rounded = e(cfg.n_ctx_vision, self.Dv)
-            self.vpt_scratch = e(cfg.n_ctx_vision, self.Dv, dt=self.fwd)
-            self.vpt_stats = (e(cfg.n_ctx_vision), e(cfg.n_ctx_vision))
-            self.vpt_gsum = e(cfg.n_ctx_vision, self.Dv)
+            nr = B * cfg.n_ctx_vision           # the shallow prompt rows of every image (layer-0 VPT gradient)
+            self.vpt_rounded = e(nr, self.Dv)
+            self.vpt_scratch = e(nr, self.Dv, dt=self.fwd)
+            self.vpt_stats = (e(nr), e(nr))
+            self.vpt_dy, self.vpt_dx = e(nr, self.Dv), e(nr, self.Dv)
 
         # ---- frozen teacher (PromptSRC): ZS image features per step, fixed text embeddings once
         if cfg.zero_shot_branch:
@@ -639,14 +640,17 @@ class PromptedClipStep:
             ops.gather_ln_bwd(self.dhv, self.vt.x_final, None, self.ln_post[0], *self.hv_stats, self.vt.dx, B,
                               self.Lv, self.Dv, dx_act=self.vt.dxa)
             self.vt.backward(self.vgrads)
-            # VPT enters before ln_pre (model.py:414-420): sum the ln_pre output grads over images, then
-            # one LayerNorm backward on the n_ctx (image-independent) rounded prompt rows
-            n = cfg.n_ctx_vision
-            ops.insert_prompt(self.vpt_rounded, self.vprompts[0], 1, n, 0, n, self.Dv, round_fp16=True)
+            # VPT enters before ln_pre as `VPT.expand(B, -1, -1).half()` (model.py:414-420): autograd runs the ln_pre
+            # backward on every image's prompt rows, casts each image's gradient through fp16 (the backward of the
+            # type promotion / `.half()`), and only then sums over the images.  Same order here: the prompt rows of
+            # d(ln_pre output) are gathered, one LayerNorm backward over the B * n_ctx rows (the rounded prompt and its
+            # statistics are the same for every image), then the per-sequence fp16 rounding + sum of psrc_prompt_grad.
+            n, P = cfg.n_ctx_vision, cfg.arch.n_patches
+            ops.insert_prompt(self.vpt_rounded, self.vprompts[0], B, n, 0, n, self.Dv, round_fp16=True)
             ops.layernorm_fwd(self.vpt_rounded, *self.ln_pre, self.vpt_scratch, *self.vpt_stats)
-            ops.prompt_grad(self.vt.dx, self.vpt_gsum, B, self.Lv, 1 + cfg.arch.n_patches, n, self.Dv,
-                            zero_rows=False, round_fp16=False)
-            ops.layernorm_bwd(self.vpt_gsum, self.vpt_rounded, self.ln_pre[0], *self.vpt_stats, self.vgrads[0])
+            self.vpt_dy.view(B, n, self.Dv).copy_(self.vt.dx.view(B, self.Lv, self.Dv)[:, 1 + P:])
+            ops.layernorm_bwd(self.vpt_dy, self.vpt_rounded, self.ln_pre[0], *self.vpt_stats, self.vpt_dx)
+            ops.prompt_grad(self.vpt_dx, self.vgrads[0], B, n, 0, n, self.Dv, zero_rows=False, round_fp16=True)
 
     def backward_from(self, g_logits, g_that=None, g_fhat=None):
         """Autograd bridge (trainers.CustomCLIP): upstream gradients of an arbitrary loss w.r.t. logits [B, C],
