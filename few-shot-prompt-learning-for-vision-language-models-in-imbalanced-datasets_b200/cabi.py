@@ -71,6 +71,7 @@ SIGNATURES = {
     "psrc_l2norm_fwd": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "psrc_l2norm_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp]),
     "psrc_loss_fwd_bwd": (_i, [C.POINTER(LossArgs), _vp]),
+    "psrc_loss_fwd_bwd_noalloc": (_i, [C.POINTER(LossArgs), _vp]),
     "psrc_sgd_step": (_i, [_vp, _vp, _vp, _vp, _f, _f, _f, _i, _i, _i64, _vp]),
     "psrc_cast": (_i, [_vp, _i, _vp, _i, _i64, _vp]),
     "psrc_axpy": (_i, [_vp, _vp, _f, _i64, _vp]),

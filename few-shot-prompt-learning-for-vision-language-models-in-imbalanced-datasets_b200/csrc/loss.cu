@@ -5,6 +5,7 @@
 // One pass over each [B,C] logits row produces its loss partials and d(loss)/d(logits).  All
 // reductions use a fixed order (deterministic); every rank of a class/batch-sharded job emits its
 // additive share of the single-device loss (divisors are the GLOBAL batch / class counts).
+#include <mutex>
 #include "common.cuh"
 
 namespace psrc {
@@ -198,4 +199,67 @@ extern "C" int psrc_loss_fwd_bwd(const psrc_loss_args* args, psrc_stream_t strea
   loss_finalize_kernel<<<1, 256, 0, s>>>(a.row_scratch, a.B, has_text, has_image, a.losses);
   PSRC_CHECK_LAUNCH();
   return PSRC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// psrc_loss_fwd_bwd_noalloc -- the same objective for callers that cannot hand over a workspace.
+//
+// psrc_loss_fwd_bwd needs a few KB of global memory (`row_scratch`) between its kernels.  Some hosts
+// of this library have no way to provide it: a plugin that is only handed the framework's input and
+// output buffers and is forbidden from calling cudaMalloc itself (a serving runtime that has already
+// pre-reserved all of the device's memory, a callback running while another thread captures a CUDA
+// graph -- cudaMalloc is illegal there --, or a real-time loop that may not take the allocator's
+// locks).  For them the workspace lives in the library image: a file-scope __device__ array that each
+// GPU gets when it loads this module and keeps until the process exits (34 KB per GPU).
+//
+// `g_loss_scratch` below is, in HOST code, only a handle for the symbol -- not a device address.  The
+// address differs per GPU and is looked up with cudaGetSymbolAddress once per device (with that
+// device current) and remembered; the kernels get the looked-up pointer through args.row_scratch.
+namespace psrc {
+
+constexpr int kNoAllocMaxRows = 4096;                                    // B limit of the entry point
+constexpr int kNoAllocFloats = 2 * kNoAllocMaxRows + 2 * kL1Blocks;      // what loss_finalize_kernel reads
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) float g_loss_scratch[kNoAllocFloats];
+
+static float* g_loss_scratch_addr[kNoAllocMaxDevices];  // device address of g_loss_scratch, per GPU ordinal
+static std::mutex g_loss_scratch_mu;
+
+// Device address of the static workspace on the CURRENT device (first use per device does the lookup).
+static int loss_scratch_for_current_device(float** out) {
+  int dev = -1;
+  PSRC_CHECK_CUDA(cudaGetDevice(&dev));
+  PSRC_CHECK_ARG(dev >= 0 && dev < kNoAllocMaxDevices,
+                 "psrc_loss_fwd_bwd_noalloc: device ordinal %d is beyond the %d this entry point keeps addresses for",
+                 dev, kNoAllocMaxDevices);
+  std::lock_guard<std::mutex> lock(g_loss_scratch_mu);
+  if (g_loss_scratch_addr[dev] == nullptr) {
+    float* p = nullptr;
+    PSRC_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_loss_scratch));
+    PSRC_CHECK_ARG(p != nullptr, "psrc_loss_fwd_bwd_noalloc: cudaGetSymbolAddress returned a null address");
+    g_loss_scratch_addr[dev] = p;
+  }
+  *out = g_loss_scratch_addr[dev];
+  return PSRC_OK;
+}
+
+}  // namespace psrc
+
+extern "C" int psrc_loss_fwd_bwd_noalloc(const psrc_loss_args* args, psrc_stream_t stream) {
+  PSRC_CHECK_ARG(args != nullptr, "psrc_loss_fwd_bwd_noalloc: null args");
+  PSRC_CHECK_ARG(args->B > 0 && args->C > 0, "psrc_loss_fwd_bwd_noalloc: bad B/C");
+  PSRC_CHECK_ARG(args->B <= kNoAllocMaxRows,
+                 "psrc_loss_fwd_bwd_noalloc: B = %d logits rows exceed the built-in workspace (at most %d rows per "
+                 "call); split the batch or use psrc_loss_fwd_bwd with a caller-owned row_scratch",
+                 args->B, kNoAllocMaxRows);
+  float* scratch = nullptr;
+  const int rc = loss_scratch_for_current_device(&scratch);
+  if (rc != PSRC_OK) return rc;
+  // Nothing in the workspace has to start at zero: every slot loss_finalize_kernel reads ([0, 2B) and,
+  // per enabled L1 term, its 148 partials) is written earlier in this same call, so what the previous
+  // call left behind is never observed.
+  psrc_loss_args with_scratch = *args;   // the caller's row_scratch (if any) is ignored
+  with_scratch.row_scratch = scratch;
+  return psrc_loss_fwd_bwd(&with_scratch, stream);
 }

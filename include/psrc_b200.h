@@ -12,6 +12,8 @@
  *   - every pointer is a DEVICE pointer unless the name ends in _host
  *   - every function is asynchronous on `stream`, stateless, re-entrant and
  *     safe to capture into a CUDA graph (no allocation, no host sync)
+ *     (this sentence does not cover psrc_loss_fwd_bwd_noalloc, which keeps a workspace inside the
+ *     library and therefore is neither stateless nor re-entrant -- read its own comment)
  *   - return value: 0 = ok, otherwise a PSRC_ERR_* code; the message for the
  *     calling thread's last error is psrc_last_error()
  *   - activations are batch-first: row r = sequence * L + position
@@ -267,6 +269,33 @@ typedef struct {
   float* row_scratch;           /* [>= 4*B + 2*296] fp32 workspace                 */
 } psrc_loss_args;
 int psrc_loss_fwd_bwd(const psrc_loss_args* args, psrc_stream_t stream);
+
+/* The same objective for hosts that have no workspace to give.  (No counterpart in the reference:
+ * PyTorch allocates freely; this exists only for embedders of this library.)
+ *
+ * Who needs it: a caller that receives nothing but its input and output buffers and is not allowed to
+ * obtain device memory itself -- a plugin inside a runtime that has already reserved the whole GPU,
+ * code that runs while some thread is capturing a CUDA graph (cudaMalloc is illegal then), or a
+ * latency-critical loop that must stay clear of the allocator's locks.  Such a caller cannot supply
+ * `row_scratch`, so here the workspace is a fixed array inside the library's device image.
+ *
+ *   - args->row_scratch is ignored (NULL is fine); everything else means what it means above, and
+ *     the results are those of the entry point above on the same inputs.
+ *   - limit: args->B <= 4096 logits rows per call (C, Ct and E are not limited -- the workspace holds
+ *     per-row and per-CTA partial sums only).  A larger B returns PSRC_ERR_ARG with a message that
+ *     names the limit; split the batch or use the entry point above.
+ *   - cost: 34 KB of device memory on every GPU that loads the library, held until the process exits.
+ *   - the call performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ *   - the FIRST call on each device looks up that device's address of the array
+ *     (cudaGetSymbolAddress, with the device current) and remembers it.  Make that first call during
+ *     start-up, with the target device current, before any stream capture begins; `stream` must belong
+ *     to the current device, as for every entry point here.
+ *   - all calls on one GPU share the one array.  It still holds the previous call's partial sums when
+ *     the next call starts; that is harmless because each call overwrites every slot before reading it
+ *     (nothing needs to start at zero).  But two calls that are in flight on the same GPU at the same
+ *     time -- different streams without an ordering between them -- overwrite each other's partial
+ *     sums and return wrong losses: run them on one stream or order them with events. */
+int psrc_loss_fwd_bwd_noalloc(const psrc_loss_args* args, psrc_stream_t stream);
 
 /* torch.optim.SGD semantics (Dassl optim/optimizer.py:105-113) on a flat buffer:
  * g += wd*p ; buf = first ? g : mom*buf + (1-damp)*g ; p -= lr*(nesterov? g+mom*buf : buf)
