@@ -21,6 +21,7 @@ def _run(extra, port):
            "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "multigpu_check.py"), *extra]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     lines = [json.loads(ln) for ln in res.stdout.splitlines() if ln.startswith("{")]
+    print("\n".join(json.dumps(ln) for ln in lines))          # shown by `pytest -rA` (profiles/r03_multigpu_pytest.log)
     assert res.returncode == 0, f"rc={res.returncode}\n{lines}\n{res.stderr[-3000:]}"
     return lines
 
@@ -40,3 +41,28 @@ def test_two_rank_step_matches_cfg3_golden(prec):
         pytest.skip("needs 2 GPUs")
     lines = _run(["--golden", "cfg3_promptsrc_ce", "--prec", prec], 29543)
     assert lines[0]["ok"] and lines[-1]["all_ranks_identical_params_and_ok"], lines
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_two_rank_captured_segments_match_eager_and_single_gpu(prec):
+    """The step the trainers and bench.py run at world_size > 1: six segment graphs in one pool with NCCL between them,
+    the batch arriving on the copy stream.  Three steps on three batches: bit-identical to the eager sharded launches
+    on every rank, and within the sharding tolerance of the captured single-GPU step (multigpu_check.py --graphs)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    lines = _run(["--classes", "1000", "--batch", "8", "--prec", prec, "--graphs"], 29545)
+    g = [ln for ln in lines if "graphs_ok" in ln]
+    assert g and g[0]["graphs_ok"] and g[0]["graph_vs_eager_param_maxabs"] == 0.0, lines
+    assert lines[-1]["all_ranks_identical_params_and_ok"], lines
+
+
+@pytest.mark.parametrize("trainer,classes", [("cocoop", "100"), ("maple", "1000")])
+def test_two_rank_captured_segments_cocoop_and_maple(trainer, classes):
+    """Same check for the pure batch-sharded CoCoOp step (one graph + all-reduce + SGD graph, `whole`) and the MaPLe
+    step (class-sharded text tower with the coupling functions' backward in the last segment)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    lines = _run(["--classes", classes, "--batch", "4", "--prec", "bf16", "--graphs", "--trainer", trainer], 29547)
+    g = [ln for ln in lines if "graphs_ok" in ln]
+    assert lines[0]["ok"] and g and g[0]["graphs_ok"], lines
+    assert lines[-1]["all_ranks_identical_params_and_ok"], lines
