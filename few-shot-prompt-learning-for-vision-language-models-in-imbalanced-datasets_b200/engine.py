@@ -79,6 +79,9 @@ class TowerWeights:
         self.need_backward = need_backward
 
 
+ROW_ATTN_MAX_L = 288    # psrc_attn_row_fwd / _bwd: 32 lanes x 9 keys per lane (csrc/attention_row.cu:22)
+
+
 class Tower:
     """A stack of residual attention blocks over ``n_seq`` sequences of length ``L``.
 
@@ -120,6 +123,11 @@ class Tower:
             self.dx = e(M, D)
             self.dxa = e(M, D, dt=dt.grad) if dt.grad != torch.float32 else None
 
+    def _row_only_last(self, i):
+        """Block i is the last one and runs in the class-token-only form.  Sequences longer than the one-query attention
+        kernels take (ViT-L/14@336px: 577 tokens) keep the ordinary full-row block -- same result on row 0, any L."""
+        return self.cls_only_last_mlp and i == self.nl - 1 and self.L <= ROW_ATTN_MAX_L
+
     # -- buffers of layer i
     def _xin(self, i):
         return self.X[i] if self.save else self.X[0]
@@ -147,7 +155,7 @@ class Tower:
             mean1, rstd1, mean2, rstd2 = self.stats[s]
             ops.layernorm_fwd(x0, b.ln1_g, b.ln1_b, self.h, mean1, rstd1)
             ops.gemm(self.h, b.wqkv, self.qkv[s], bias=b.bqkv)
-            if self.cls_only_last_mlp and i == self.nl - 1:
+            if self._row_only_last(i):
                 # Last block, consumer reads row 0 only: every token's K / V still feed the class-token query, so LN1
                 # and the q/k/v projection run on all rows; the attention core runs for ONE query per (sequence,
                 # head), and the out-projection, LN2 and the MLP on the n_seq class-token rows, addressed as strided
@@ -180,7 +188,7 @@ class Tower:
         for i in range(self.nl - 1, stop_at_layer - 1, -1):
             b = self.w.blocks[i]
             mean1, rstd1, mean2, rstd2 = self.stats[i]
-            if self.cls_only_last_mlp and i == self.nl - 1:
+            if self._row_only_last(i):
                 # the incoming gradient is non-zero on the class-token rows only (it came through gather_ln_bwd with
                 # idx = None, which zeroes every other row of dx / dxa): the MLP branch and the out-projection are
                 # differentiated on those n_seq rows; d(attention output) of every other row is zero

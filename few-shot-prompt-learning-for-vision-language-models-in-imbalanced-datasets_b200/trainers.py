@@ -396,9 +396,12 @@ class _CustomCLIPBase(nn.Module):
             world, rank, pg = dist.get_world_size(), dist.get_rank(), dist.group.WORLD
         # Dassl drops the last short batch only when the train set holds at least one full batch
         # (data_manager.py:37-48): a few-shot set SMALLER than BATCH_SIZE arrives as one short batch every iteration,
-        # and the reference trains on it -- the trainer passes that size in (_PromptTrainer._train_batch_size)
-        global _BATCH_OVERRIDE
-        batch_size, _BATCH_OVERRIDE = (_BATCH_OVERRIDE or int(cfg.DATALOADER.TRAIN_X.BATCH_SIZE)), None
+        # and the reference trains on it -- the trainer passes that size in (`train_batch`, _PromptTrainer._train_batch_size)
+        batch_size = int(step_kwargs.pop("train_batch", None) or cfg.DATALOADER.TRAIN_X.BATCH_SIZE)
+        if batch_size % world != 0:
+            raise RuntimeError(f"the training batch of {batch_size} images does not split over {world} ranks: every rank "
+                               "takes an equal contiguous share of the batch Dassl's loader delivers "
+                               "(choose BATCH_SIZE / the shot count as a multiple of the world size)")
         scfg = StepConfig(arch=arch, n_cls=tokens.shape[0], batch=batch_size // world,
                           prec=prec, world_size=world, rank=rank, process_group=pg, **step_kwargs)
         self._step = PromptedClipStep(scfg, sd, tokens, dev, fixed_embeddings=fixed_embeddings)
@@ -486,6 +489,9 @@ class _CustomCLIPBase(nn.Module):
         if w > 1 and image.shape[0] == st.cfg.batch * w:
             # Dassl's loader has no DistributedSampler: every rank is handed the full BATCH_SIZE (same seed, same
             # order) -- each rank trains on its contiguous share, as the sharded step expects
+            if not getattr(self, "_ranks_share_batch", False):
+                self.check_ranks_share_the_batch(label)          # first step only: one 16-byte all-gather
+                self._ranks_share_batch = True
             lo = st.cfg.rank * st.cfg.batch
             image, label = image[lo:lo + st.cfg.batch], label[lo:lo + st.cfg.batch]
             next_batch = None
@@ -518,6 +524,22 @@ class _CustomCLIPBase(nn.Module):
         if self._infer is not None:
             self._infer.text_valid = False
         return st.losses
+
+    def check_ranks_share_the_batch(self, label):
+        """Slicing the full batch by rank is only a partition of it when every rank's Dassl loader drew the SAME batch.
+        Dassl seeds its samplers only for cfg.SEED >= 0 (dassl/utils/tools.py:set_random_seed, called from train.py
+        when a seed is given; the default is -1): unseeded ranks shuffle differently, and an epoch then visits some
+        samples twice and others never.  Compare a fingerprint of the labels across ranks and refuse to go on."""
+        import torch.distributed as dist
+        st = self._step
+        lab = label.detach().to("cpu", torch.int64).flatten()
+        fp = torch.stack([lab.sum(), (lab * torch.arange(1, lab.numel() + 1)).sum()]).to(st.device)
+        got = [torch.empty_like(fp) for _ in range(st.cfg.world_size)]
+        dist.all_gather(got, fp, group=st.cfg.process_group)
+        if any(not torch.equal(g, got[0]) for g in got):
+            raise RuntimeError("the ranks received different training batches, so slicing the batch by rank would not "
+                               "partition it: give every rank the same seed >= 0 (train.py --seed / cfg.SEED; Dassl "
+                               "leaves its samplers unseeded for the default -1)")
 
     def step_loss(self, losses) -> float:
         """`loss.item()` of the fused step (promptsrc.py:330): read from the pinned copy made right after the step, so the
@@ -555,7 +577,7 @@ class PromptSRCCustomCLIP(_CustomCLIPBase):
     teacher of promptsrc_pets_focal.py:165-175), `fixed_embeddings`."""
 
     def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, teacher_tokens=None,
-                 fixed_embeddings=None, device=None):
+                 fixed_embeddings=None, device=None, train_batch=None):
         super().__init__()
         T = cfg.TRAINER.PROMPTSRC
         assert T.PROMPT_DEPTH_TEXT >= 1, "Language prompt depth should be >= 1 (promptsrc.py:77-80)"
@@ -595,6 +617,7 @@ class PromptSRCCustomCLIP(_CustomCLIPBase):
                   w_logits=float(_get(T, "LOGITS_LOSS_WEIGHT", 1.0)))      # key missing upstream
         if _get(T, "LOSS_TYPE", "ce") == "focal":                            # promptsrc_pets_focal.py:230-247
             kw["focal_alpha"] = _focal_alpha_from_cfg(cfg, len(classnames))
+        kw["train_batch"] = train_batch
         self._build(cfg, clip_model, tokens, kw, ctx_vectors, fixed_embeddings=fixed_embeddings, device=dev)
         self.prompt_learner.fixed_embeddings = fixed_embeddings.to(dev)
         self.total_epochs = cfg.OPTIM.MAX_EPOCH
@@ -618,7 +641,7 @@ def _focal(logits, label, st):
 class CoOpCustomCLIP(_CustomCLIPBase):
     """CustomCLIP of trainers/coop.py:302-390 for LOSS_TYPE ce / focal, CLASS_TOKEN_POSITION end / middle / front."""
 
-    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None):
+    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None, train_batch=None):
         super().__init__()
         T = cfg.TRAINER.COOP
         self.cfg = cfg
@@ -650,6 +673,7 @@ class CoOpCustomCLIP(_CustomCLIPBase):
                   ctx_per_class=csc, zero_shot_branch=False, class_token_position=position)
         if self.loss_type == "focal":
             kw["focal_alpha"] = _focal_alpha_from_cfg(cfg, len(classnames))
+        kw["train_batch"] = train_batch
         self._build(cfg, clip_model, tokens, kw, ctx_vectors, device=device)
 
     def forward_once(self, image):
@@ -699,7 +723,7 @@ class _MaPLePromptLearner(nn.Module):
 class MaPLeCustomCLIP(_CustomCLIPBase):
     """CustomCLIP of trainers/maple.py:206-255 (CE or focal loss, :221-238)."""
 
-    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None):
+    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None, train_batch=None):
         super().__init__()
         T = cfg.TRAINER.MAPLE
         self.cfg = cfg
@@ -725,6 +749,7 @@ class MaPLeCustomCLIP(_CustomCLIPBase):
                   coupling=True, zero_shot_branch=False)
         if self.use_focal_loss:
             kw["focal_alpha"] = _focal_alpha_from_cfg(cfg, len(classnames))
+        kw["train_batch"] = train_batch
         self._build(cfg, clip_model, tokens, kw, ctx_vectors, device=device)
 
     def _make_prompt_learner(self, scfg, ctx_init, prefix, suffix, tokens):
@@ -775,7 +800,7 @@ class CoCoOpCustomCLIP(_CustomCLIPBase):
     """CustomCLIP of trainers/cocoop.py:200-260 (CE or focal loss, :214-233).  The meta-net stays fp32 whatever
     PREC says (the reference's `.half()` at :146-147 cannot run on its fp32 model)."""
 
-    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None):
+    def __init__(self, cfg, classnames, clip_model, tokenized_prompts=None, device=None, train_batch=None):
         super().__init__()
         T = cfg.TRAINER.COCOOP
         self.cfg = cfg
@@ -802,6 +827,7 @@ class CoCoOpCustomCLIP(_CustomCLIPBase):
                   per_image_text=True, meta_hidden=vis_dim // 16, zero_shot_branch=False)
         if self.use_focal_loss:
             kw["focal_alpha"] = _focal_alpha_from_cfg(cfg, len(classnames))
+        kw["train_batch"] = train_batch
         self._build(cfg, clip_model, tokens, kw, ctx_vectors, device=device)
 
     def _make_prompt_learner(self, scfg, ctx_init, prefix, suffix, tokens):
@@ -833,7 +859,6 @@ def _load_clip(cfg, trainer_name):
     return mod.load_clip_to_cpu(cfg)
 
 
-_BATCH_OVERRIDE = None      # set by the trainer for the next CustomCLIP it builds (train set smaller than BATCH_SIZE)
 CLIP_MODEL_FACTORY = None   # callable(cfg, trainer_name) -> reference-keyed CLIP module (fp32)
 TOKEN_FACTORY = None        # callable(cfg, classnames) -> int64 [C, 77] tokenised prompts, or None for the reference tokenizer
 
@@ -842,13 +867,14 @@ class _PromptTrainer(TrainerX):
     MODEL_NAME = "prompt_learner"
 
     def _tokens(self, classnames):
-        """Called right before the CustomCLIP is built: also tells `_build` the batch size the loader will deliver."""
-        global _BATCH_OVERRIDE
+        return TOKEN_FACTORY(self.cfg, classnames) if TOKEN_FACTORY is not None else None
+
+    def _train_batch_size(self):
+        """The batch size Dassl's train loader will deliver: BATCH_SIZE, or -- a train set SMALLER than BATCH_SIZE -- the
+        whole set as one short batch per epoch, which is not dropped (data_manager.py:37-48).  None = cfg's BATCH_SIZE."""
         bs = int(self.cfg.DATALOADER.TRAIN_X.BATCH_SIZE)
         train_x = getattr(getattr(self.dm, "dataset", None), "train_x", None)
-        if train_x is not None and 0 < len(train_x) < bs:
-            _BATCH_OVERRIDE = len(train_x)            # one short batch per epoch, not dropped (data_manager.py:37-48)
-        return TOKEN_FACTORY(self.cfg, classnames) if TOKEN_FACTORY is not None else None
+        return len(train_x) if train_x is not None and 0 < len(train_x) < bs else None
 
     def _init_weights(self, module):
         """`if cfg.MODEL.INIT_WEIGHTS: load_pretrained_weights(self.model, ...)` of every reference build_model
@@ -951,7 +977,7 @@ class PromptSRC(_PromptTrainer):
         clip_model = _load_clip(cfg, "PromptSRC")
         clip_model.float()
         self.model = PromptSRCCustomCLIP(cfg, classnames, clip_model, tokenized_prompts=self._tokens(classnames),
-                                         device=self.device)
+                                         device=self.device, train_batch=self._train_batch_size())
         self._finish_build(self.model)
         self.total_epochs = cfg.OPTIM.MAX_EPOCH
         self.step_counter = 1
@@ -1005,7 +1031,7 @@ class CoOp(_PromptTrainer):
         clip_model = _load_clip(cfg, "CoOp")
         clip_model.float()
         self.model = CoOpCustomCLIP(cfg, classnames, clip_model, tokenized_prompts=self._tokens(classnames),
-                                    device=self.device)
+                                    device=self.device, train_batch=self._train_batch_size())
         self._finish_build(self.model.prompt_learner)                        # coop.py:431
 
     def forward_backward(self, batch):
@@ -1038,7 +1064,7 @@ class MaPLe(_PromptTrainer):
         clip_model = _load_clip(cfg, "MaPLe")
         clip_model.float()
         self.model = MaPLeCustomCLIP(cfg, classnames, clip_model, tokenized_prompts=self._tokens(classnames),
-                                     device=self.device)
+                                     device=self.device, train_batch=self._train_batch_size())
         self._finish_build(self.model)                                       # maple.py:301 registers the whole model
 
     def forward_backward(self, batch):
@@ -1064,7 +1090,7 @@ class CoCoOp(_PromptTrainer):
         clip_model = _load_clip(cfg, "CoCoOp")
         clip_model.float()
         self.model = CoCoOpCustomCLIP(cfg, classnames, clip_model, tokenized_prompts=self._tokens(classnames),
-                                      device=self.device)
+                                      device=self.device, train_batch=self._train_batch_size())
         self._finish_build(self.model.prompt_learner)                        # cocoop.py:304
 
     def forward_backward(self, batch):

@@ -183,7 +183,7 @@ def test_train_set_smaller_than_batch_size_builds_the_step_for_the_short_batch(m
     monkeypatch.setattr(TC, "FakeDM", SmallDM)
     tr, cfg, tokens = TC.make_trainer("PromptSRC", "fp32", device="cpu")
     assert cfg.DATALOADER.TRAIN_X.BATCH_SIZE == 3 and tr.model._step.cfg.batch == 2
-    assert T._BATCH_OVERRIDE is None                                  # consumed by the build
+    assert not hasattr(T, "_BATCH_OVERRIDE")     # the size travels as an explicit constructor argument, no module state
     monkeypatch.setattr(TC, "FakeDM", real_dm)
     tr2, _, _ = TC.make_trainer("PromptSRC", "fp32", device="cpu")
     assert tr2.model._step.cfg.batch == 3

@@ -45,3 +45,47 @@ def test_empty_and_single_row_inputs_through_the_c_abi():
     ops.attn_row_fwd(qkv, o2, lse, 1, 1, 1, False)
     assert torch.allclose(o2.float(), qkv[:, 128:].float(), atol=1e-2)
     torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("L", [280, 300])
+def test_class_token_only_last_block_matches_full_block_also_beyond_the_one_query_kernel_limit(L):
+    """A tower whose consumer reads the class-token row only runs its last block on that row (one-query attention,
+    L <= 288).  Longer sequences (ViT-L/14@336px has 577 tokens, `clip._MODELS`) must fall back to the full-row block
+    instead of failing in psrc_attn_row_*: both settings of `cls_only_last_mlp` give the same row 0 and the same
+    input-gradient at L = 280 (one-query kernels) and at L = 300 (fallback)."""
+    if not torch.cuda.is_available():
+        pytest.fail("CUDA device required: this package has no CPU fallback")
+    from psrc_b200.engine import Tower, TowerWeights
+    dev, D, H, n_seq, nl = torch.device("cuda"), 64, 1, 3, 2
+    g = torch.Generator().manual_seed(3)
+    r = lambda *s, sc=0.05: torch.randn(*s, generator=g) * sc  # noqa: E731
+    sd = {}
+    for i in range(nl):
+        p = f"t.resblocks.{i}."
+        sd.update({p + "ln_1.weight": 1 + r(D), p + "ln_1.bias": r(D), p + "ln_2.weight": 1 + r(D), p + "ln_2.bias": r(D),
+                   p + "attn.in_proj_weight": r(3 * D, D, sc=0.1), p + "attn.in_proj_bias": r(3 * D),
+                   p + "attn.out_proj.weight": r(D, D, sc=0.1), p + "attn.out_proj.bias": r(D),
+                   p + "mlp.c_fc.weight": r(4 * D, D, sc=0.1), p + "mlp.c_fc.bias": r(4 * D),
+                   p + "mlp.c_proj.weight": r(D, 4 * D, sc=0.1), p + "mlp.c_proj.bias": r(D)})
+    w = TowerWeights(sd, "t.", nl, dev, torch.bfloat16, need_backward=True)
+    x0 = r(n_seq * L, D, sc=1.0).to(dev)
+    d_cls = r(n_seq, D, sc=1.0).to(dev)
+    outs = []
+    for flag in (False, True):
+        t = Tower(w, n_seq, L, D, H, False, True, dev)
+        t.cls_only_last_mlp = flag
+        t.x0.copy_(x0)
+        y = t.forward().view(n_seq, L, D)[:, 0].clone()
+        t.dx.zero_()
+        t.dx.view(n_seq, L, D)[:, 0] = d_cls          # the gradient enters on the class-token rows only
+        t.dxa.copy_(t.dx)
+        dx = t.backward().clone()
+        torch.cuda.synchronize()
+        outs.append((y, dx))
+    (y0, dx0), (y1, dx1) = outs
+    assert torch.isfinite(y1).all() and torch.isfinite(dx1).all()
+    if L > 288:     # same launches either way
+        assert torch.equal(y0, y1) and torch.equal(dx0, dx1)
+    else:           # one-query kernels vs the full attention kernels: bf16 rounding of different summation orders
+        assert float((y0 - y1).abs().max()) <= 2e-2 * float(y0.abs().max())
+        assert float(torch.nn.functional.cosine_similarity(dx0.flatten(), dx1.flatten(), dim=0)) >= 0.999

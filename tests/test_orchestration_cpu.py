@@ -305,7 +305,13 @@ def _trainer_worker(rank, world, port, out):
         for s_ in range(2):                       # Dassl hands EVERY rank the full batch (no DistributedSampler)
             tr.batch_idx = 0
             losses.append(tr.forward_backward({"img": image, "label": label})["loss"])
-        out[rank] = {"losses": losses, "param": tr.model._step.flat_param.clone()}
+        assert tr.model._ranks_share_batch        # the first step compared the ranks' label fingerprints
+        try:                                      # unseeded loaders: every rank holds another batch -> refused
+            tr.model.check_ranks_share_the_batch(label + rank)
+            refused = False
+        except RuntimeError as ex:
+            refused = "seed" in str(ex)
+        out[rank] = {"losses": losses, "param": tr.model._step.flat_param.clone(), "refused": refused}
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -331,5 +337,6 @@ def test_trainer_level_two_ranks_slice_the_full_batch_and_match_one_process(monk
     ref = tr.model._step.flat_param
     assert float((out[0]["param"] - out[1]["param"]).abs().max()) == 0.0
     for r in range(world):
+        assert out[r]["refused"], "ranks holding different batches must be refused (ADVICE r2)"
         assert max(abs(a - b) for a, b in zip(out[r]["losses"], ref_losses)) < 1e-5, (out[r]["losses"], ref_losses)
         assert float((out[r]["param"] - ref).abs().max()) < 1e-7, float((out[r]["param"] - ref).abs().max())
