@@ -9,7 +9,16 @@ sampled window; resampling, flip, /255 and normalisation run in one CUDA launch 
 Index / label / parameter flow is bit-identical to the reference: `rrc_params` and `flip_param` make exactly the torch
 RNG calls torchvision's `RandomResizedCrop.get_params` and `RandomHorizontalFlip.forward` make, in the same order
 (checked against torchvision in tests/test_input_pipeline_cpu.py).  Pixels are not bit-identical to PIL (float weights
-instead of PIL's 8-bit fixed point): <= 1 grey level on nearly every pixel, gated in the tests.
+instead of PIL's 8-bit fixed point): <= 1 grey level on nearly every pixel, gated in the tests -- AS LONG AS the sampled
+window fits the canvas.  A window larger than the canvas is first shrunk by an integer box filter (`_reduce`), which
+the reference's PIL `resize` does not do; measured against the reference's PIL output on noisy synthetic images
+(tests/test_input_pipeline_cpu.py::test_canvas_reduction_deviation_from_pil_is_bounded):
+  - the shrunk window is still larger than the output (768 x 1024 image on the default 512 canvas): mean 0.8, max 5 levels;
+  - the shrunk window falls below the output size and is scaled up again (a 330 x 370 window on a 256 canvas ->
+    165 x 185 -> 224): mean 3, max 24 grey levels.  A 256 canvas does this to ordinary ImageNet-sized images, so the
+    default canvas is 512 x 512 (786 KB per image over PCIe, more than the 602 KB of the fp32 tensor: the gain left is
+    the resampling work taken off the loader processes).  Choose a smaller canvas only for datasets whose images fit
+    it (CIFAR-sized sets, pre-shrunk caches) or when that pixel error is acceptable.
 
     tfm = DeviceTransform(size=224, is_train=True)                 # use as Dassl `custom_tfm_train`
     item = tfm(pil_image)          -> {"u8": uint8 [Hc, Wc, 3], "geom_f": fp32 [4], "geom_i": int32 [5]}
@@ -96,12 +105,12 @@ class DeviceTransform:
     worker, it draws the augmentation parameters and returns the uint8 window + geometry instead of a float tensor."""
 
     def __init__(self, size=224, is_train=True, scale=(0.08, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0), flip_p=0.5,
-                 canvas=(256, 256), random_flip=True):
+                 canvas=(512, 512), random_flip=True):
         self.size, self.is_train, self.scale, self.ratio = int(size), bool(is_train), tuple(scale), tuple(ratio)
         self.flip_p, self.canvas, self.random_flip = flip_p, tuple(canvas), random_flip
 
     @classmethod
-    def from_cfg(cls, cfg, is_train=True, canvas=(256, 256)):
+    def from_cfg(cls, cfg, is_train=True, canvas=(512, 512)):
         """Same cfg keys as transforms.py:176-243; only the PromptSRC-family choices are expressible on the device."""
         choices = list(cfg.INPUT.TRANSFORMS)
         known = {"random_resized_crop", "random_flip", "normalize"}
@@ -152,7 +161,7 @@ class DevicePreprocessor:
     has been launched (it waits for that kernel only, not for the step that follows it) -- the same look-ahead contract
     as `PromptedClipStep.stage_host`."""
 
-    def __init__(self, device, batch, size=224, canvas=(256, 256), interpolation="bicubic", quantize=2,
+    def __init__(self, device, batch, size=224, canvas=(512, 512), interpolation="bicubic", quantize=2,
                  mean=CLIP_MEAN, std=CLIP_STD):
         self.device, self.batch, self.size = torch.device(device), batch, size
         self.interp, self.quantize, self.mean, self.std = INTERPOLATION[interpolation], int(quantize), mean, std
