@@ -850,16 +850,23 @@ class PromptedClipStep:
         H2D of the uint8 windows (a third of the fp32 batch at 256 x 256 canvases) -> crop / bicubic resample / flip /
         normalise kernel into self.image -> step -> SGD -> loss.  `next_host = (item, labels)` starts the following
         batch's copies under this step's compute."""
+        self.run_host_u8(item, label_host, next_host=next_host, canvas=canvas)
+        return self.loss_value()
+
+    def run_host_u8(self, item: dict, label_host: torch.Tensor, next_host=None, canvas=None):
+        """`train_step_host_u8` without the final loss read (the trainers read it through `loss_value()` later).
+        `self.input_kwargs` (mean / std / interpolation of cfg.INPUT) configures the preprocessor on first use."""
         pre = getattr(self, "_pre", None)
         if pre is None:
             from .input_pipeline import DevicePreprocessor
             pre = self._pre = DevicePreprocessor(self.device, self.cfg.batch, self.cfg.arch.image_resolution,
-                                                 canvas=canvas or tuple(item["u8"].shape[1:3]))
+                                                 canvas=canvas or tuple(item["u8"].shape[1:3]),
+                                                 **getattr(self, "input_kwargs", {}))
         pre.run(item, self.image, labels_out=self.labels, label_host=label_host)
         self.run()
         if next_host is not None:
             pre.stage(*next_host)
-        return self.loss_value()
+        return self.losses
 
     def stage_host(self, image_host: torch.Tensor, label_host: torch.Tensor):
         """Start the H2D copy of the NEXT batch into staging buffers on the copy stream and return at once."""

@@ -106,6 +106,9 @@ except Exception:  # noqa: BLE001 - any import problem means "no Dassl here"
         def parse_batch_train(self, batch):
             return batch["img"].to(self.device), batch["label"].to(self.device)
 
+        def parse_batch_test(self, batch):                                   # dassl/engine/trainer.py:491-498
+            return batch["img"].to(self.device), batch["label"].to(self.device)
+
         def save_model(self, epoch, directory, is_best=False, val_result=None, model_name=""):
             import os
             for n in self.get_model_names():
@@ -486,6 +489,8 @@ class _CustomCLIPBase(nn.Module):
         prompt-only backward + SGD, and the loss terms left on the device (`.item()` is the caller's sync)."""
         st = self._step
         w = st.cfg.world_size
+        if isinstance(image, dict):          # TRAINER.B200.DEVICE_INPUT: uint8 windows + crop geometry (SURVEY 8f-4)
+            return self._train_step_fused_u8(image, label, optim, next_batch)
         if w > 1 and image.shape[0] == st.cfg.batch * w:
             # Dassl's loader has no DistributedSampler: every rank is handed the full BATCH_SIZE (same seed, same
             # order) -- each rank trains on its contiguous share, as the sharded step expects
@@ -498,18 +503,7 @@ class _CustomCLIPBase(nn.Module):
         if image.shape[0] != st.cfg.batch:
             raise RuntimeError(f"training batch {image.shape[0]} != configured per-rank batch {st.cfg.batch} "
                                "(Dassl's train loader drops the last short batch, data_manager.py:42)")
-        optim.sync_lr()
-        if self._use_graph and getattr(st, "_graph", None) is None and getattr(st, "_seg_graphs", None) is None \
-                and self._eager_steps >= 1:
-            st.capture(warmup=1)
-        self._eager_steps += 1
-        # any torch-level in-place write to a trainable tensor (load_state_dict on a sub-module, a foreign optimizer,
-        # re-initialisation) bumps its version counter, the fused SGD kernel does not -- a text prefix enqueued
-        # ahead with the old values must then be recomputed
-        ver = sum(p._version for _, p in self._named_prompts)
-        if ver != getattr(self, "_param_version", None):
-            st.invalidate_text()
-            self._param_version = ver
+        self._before_fused_step(optim)
         if image.is_cuda or st.device.type != "cuda":     # (CPU: host-logic tests over restated kernels only)
             st.image.copy_(image, non_blocking=True)
             st.labels.copy_(label.to(torch.int32), non_blocking=True)
@@ -524,6 +518,60 @@ class _CustomCLIPBase(nn.Module):
         if self._infer is not None:
             self._infer.text_valid = False
         return st.losses
+
+    def _before_fused_step(self, optim):
+        st = self._step
+        optim.sync_lr()
+        if self._use_graph and getattr(st, "_graph", None) is None and getattr(st, "_seg_graphs", None) is None \
+                and self._eager_steps >= 1:
+            st.capture(warmup=1)
+        self._eager_steps += 1
+        # any torch-level in-place write to a trainable tensor (load_state_dict on a sub-module, a foreign optimizer,
+        # re-initialisation) bumps its version counter, the fused SGD kernel does not -- a text prefix enqueued
+        # ahead with the old values must then be recomputed
+        ver = sum(p._version for _, p in self._named_prompts)
+        if ver != getattr(self, "_param_version", None):
+            st.invalidate_text()
+            self._param_version = ver
+
+    def _train_step_fused_u8(self, item, label, optim, next_batch=None):
+        """`train_step_fused` for batches collated from `input_pipeline.DeviceTransform` items ({"u8", "geom_f",
+        "geom_i"}): the uint8 windows cross PCIe, `psrc_crop_resize_normalize` writes the step's fp32 image buffer, then
+        the same graph replay.  The following batch's copies are started under this step (LookaheadLoader)."""
+        st = self._step
+        w, b = st.cfg.world_size, st.cfg.batch
+        if w > 1 and item["u8"].shape[0] == b * w:
+            if not getattr(self, "_ranks_share_batch", False):
+                self.check_ranks_share_the_batch(label)
+                self._ranks_share_batch = True
+            lo = st.cfg.rank * b
+            item = {k: v[lo:lo + b].contiguous() for k, v in item.items()}
+            label, next_batch = label[lo:lo + b], None
+        if item["u8"].shape[0] != b:
+            raise RuntimeError(f"training batch {item['u8'].shape[0]} != configured per-rank batch {b} "
+                               "(Dassl's train loader drops the last short batch, data_manager.py:42)")
+        self._before_fused_step(optim)
+        st.input_kwargs = getattr(self, "input_kwargs", {})
+        ok_next = next_batch is not None and isinstance(next_batch[0], dict) and next_batch[0]["u8"].shape[0] == b
+        st.run_host_u8(item, label, next_host=next_batch if ok_next else None)
+        if self._infer is not None:
+            self._infer.text_valid = False
+        return st.losses
+
+    def images_from_u8(self, item):
+        """{"u8", "geom_f", "geom_i"} (any batch size: evaluation, the autograd-bridged forward) -> normalised fp32
+        [B, 3, R, R] on the device, one launch of `psrc_crop_resize_normalize`."""
+        from . import ops as _ops
+        from .input_pipeline import CLIP_MEAN, CLIP_STD, INTERPOLATION, max_taps
+        st, kw = self._step, getattr(self, "input_kwargs", {})
+        interp = INTERPOLATION[kw.get("interpolation", "bicubic")]
+        dev, R = st.device, st.cfg.arch.image_resolution
+        u8, gf, gi = (item[k].to(dev, non_blocking=True).contiguous() for k in ("u8", "geom_f", "geom_i"))
+        out = torch.empty(u8.shape[0], 3, R, R, device=dev)
+        _ops.crop_resize_normalize(u8, gf, gi, out, interp, int(kw.get("quantize", 2)),
+                                   max_taps(item["geom_f"].cpu().numpy(), interp), kw.get("mean", CLIP_MEAN),
+                                   kw.get("std", CLIP_STD))
+        return out
 
     def check_ranks_share_the_batch(self, label):
         """Slicing the full batch by rank is only a partition of it when every rank's Dassl loader drew the SAME batch.
@@ -624,6 +672,8 @@ class PromptSRCCustomCLIP(_CustomCLIPBase):
         self.cfg = cfg
 
     def forward(self, image, label=None):
+        if isinstance(image, dict):
+            image = self.images_from_u8(image)
         if not self.prompt_learner.training:
             return self._eval_logits(image)                                  # promptsrc.py:212-213
         st = self._step
@@ -680,6 +730,8 @@ class CoOpCustomCLIP(_CustomCLIPBase):
         return self._bridged(image.float())[0]
 
     def forward(self, img1, lbl=None, img2=None):
+        if isinstance(img1, dict):
+            img1 = self.images_from_u8(img1)
         if self._is_inference(lbl):
             return self._eval_logits(img1)
         logits = self.forward_once(img1)
@@ -764,6 +816,8 @@ class MaPLeCustomCLIP(_CustomCLIPBase):
         return named
 
     def forward(self, image, label=None):
+        if isinstance(image, dict):
+            image = self.images_from_u8(image)
         if self._is_inference(label):
             return self._eval_logits(image)
         logits = self._bridged(image.float())[0]
@@ -839,6 +893,8 @@ class CoCoOpCustomCLIP(_CustomCLIPBase):
                 ("meta.w2", m.linear2.weight), ("meta.b2", m.linear2.bias)]
 
     def forward(self, image, label=None):
+        if isinstance(image, dict):
+            image = self.images_from_u8(image)
         if self._is_inference(label):
             return self._eval_logits(image)
         logits = self._bridged(image.float())[0]
@@ -913,9 +969,40 @@ class _PromptTrainer(TrainerX):
         self.optim = self.model.make_optimizer(cfg.OPTIM)                    # SGD of optim/optimizer.py:105-113
         self.sched = build_scheduler(self.optim, cfg.OPTIM)
         self.register_model(self.MODEL_NAME, registered_module, self.optim, self.sched)
+        self.model.input_kwargs = self._input_kwargs()                  # cfg.INPUT.* for the on-device input pipeline
         loader = getattr(self, "train_loader_x", None)                  # built before the model (trainer.py:325)
         if loader is not None and not isinstance(loader, LookaheadLoader) and _get(cfg, "TRAINER.B200.LOOKAHEAD", True):
             self.train_loader_x = LookaheadLoader(loader)
+
+    def build_data_loader(self):
+        """`TRAINER.B200.DEVICE_INPUT = True`: Dassl's own DataManager (datasets, samplers, loaders, worker processes
+        unchanged -- dassl/engine/trainer.py:341-358) with `input_pipeline.DeviceTransform` as `custom_tfm_train` /
+        `custom_tfm_test` (data_manager.py:64-85): the workers draw the reference's augmentation parameters and return
+        the uint8 window, the resampling runs on the GPU.  `TRAINER.B200.DEVICE_INPUT_CANVAS` (default 512) bounds the
+        window; see input_pipeline.py for what happens to larger ones.  Default False = the reference's PIL chain."""
+        cfg = self.cfg
+        if not bool(_get(cfg, "TRAINER.B200.DEVICE_INPUT", False)):
+            return super().build_data_loader()
+        import dassl.engine.trainer as _dtr            # the name SimpleTrainer.build_data_loader itself resolves
+        from .input_pipeline import DeviceTransform
+        c = int(_get(cfg, "TRAINER.B200.DEVICE_INPUT_CANVAS", 512))
+        dm = _dtr.DataManager(cfg, custom_tfm_train=DeviceTransform.from_cfg(cfg, True, canvas=(c, c)),
+                              custom_tfm_test=DeviceTransform.from_cfg(cfg, False, canvas=(c, c)))
+        self.train_loader_x, self.train_loader_u = dm.train_loader_x, dm.train_loader_u
+        self.val_loader, self.test_loader = dm.val_loader, dm.test_loader
+        self.num_classes, self.num_source_domains, self.lab2cname = dm.num_classes, dm.num_source_domains, dm.lab2cname
+        self.dm = dm
+
+    def _input_kwargs(self):
+        cfg = self.cfg
+        kw = {"interpolation": str(_get(cfg, "INPUT.INTERPOLATION", "bicubic"))}
+        if "normalize" in list(_get(cfg, "INPUT.TRANSFORMS", ["normalize"])):
+            mean, std = _get(cfg, "INPUT.PIXEL_MEAN", None), _get(cfg, "INPUT.PIXEL_STD", None)
+            if mean is not None and std is not None:
+                kw.update(mean=tuple(float(v) for v in mean), std=tuple(float(v) for v in std))
+        else:
+            kw.update(mean=(0.0, 0.0, 0.0), std=(1.0, 1.0, 1.0))
+        return kw
 
     def model_inference(self, input):
         return self.model(input)
@@ -923,6 +1010,11 @@ class _PromptTrainer(TrainerX):
     def parse_batch_train(self, batch):
         # no `.to(device)` round trip: the fused step copies the (pinned) host batch straight into its buffers
         return batch["img"], batch["label"]
+
+    def parse_batch_test(self, batch):
+        if isinstance(batch["img"], dict):             # DEVICE_INPUT: the model turns the uint8 windows into images
+            return batch["img"], batch["label"].to(self.device)
+        return super().parse_batch_test(batch)
 
     def save_model(self, epoch, directory, is_best=False, val_result=None, model_name=""):
         """Dassl's save_model (trainer.py:118-145) writes the registered module's whole state_dict -- for PromptSRC /

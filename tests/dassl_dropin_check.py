@@ -61,8 +61,11 @@ def batches(n, bs, seed):
 class StubDataManager:
     """What SimpleTrainer.build_data_loader reads from dassl.data.DataManager (trainer.py:341-358)."""
 
+    last_kwargs = None      # what the trainer's build_data_loader passed (custom_tfm_train / custom_tfm_test)
+
     def __init__(self, cfg, *a, **k):
         from psrc_b200 import synthetic as S  # noqa: F401
+        StubDataManager.last_kwargs = dict(k)
         self.train_loader_x = batches(2, 3, seed=1)
         self.train_loader_u, self.val_loader = None, None
         test = batches(1, 5, seed=50) + batches(1, 2, seed=60)           # a ragged last test batch
@@ -173,6 +176,25 @@ def run(trainer_name: str) -> dict:
                 torch.load = _load
             ref_after = {k: v.detach() for k, v in ref.model.named_parameters() if v.requires_grad}
             m["ref_loaded_our_ckpt_maxabs"] = max(float((ref_after[k] - ours_named[k]).abs().max()) for k in ref_named)
+        # TRAINER.B200.DEVICE_INPUT: the same Dassl DataManager, handed the on-device input pipeline's transforms
+        # (data_manager.py:64-85) -- and nothing else changes (without the flag no custom transform is passed)
+        m["default_datamanager_kwargs"] = sorted(StubDataManager.last_kwargs)
+        from yacs.config import CfgNode
+        from psrc_b200.input_pipeline import DeviceTransform
+        cfg_dev = make_cfg(trainer_name, d_ours)
+        cfg_dev.defrost()
+        cfg_dev.TRAINER.B200 = CfgNode({"DEVICE_INPUT": True, "DEVICE_INPUT_CANVAS": 96})
+        cfg_dev.INPUT.TRANSFORMS = ("random_resized_crop", "random_flip", "normalize")     # the PromptSRC yamls' chain
+        with R.cpu_patches(half_roundtrip=(trainer_name == "PromptSRC")), contextlib.redirect_stdout(quiet):
+            dev_tr = build_trainer(cfg_dev)
+        k = StubDataManager.last_kwargs
+        tr_, te_ = k.get("custom_tfm_train"), k.get("custom_tfm_test")
+        m["device_input_transforms"] = bool(isinstance(tr_, DeviceTransform) and isinstance(te_, DeviceTransform)
+                                            and tr_.is_train and not te_.is_train and tr_.canvas == (96, 96)
+                                            and tr_.size == 64 and te_.size == 64)
+        m["device_input_loader_attrs"] = all(hasattr(dev_tr, a) for a in ("train_loader_x", "test_loader", "num_classes",
+                                                                         "lab2cname", "dm"))
+        m["device_input_norm"] = list(dev_tr.model.input_kwargs.get("mean", ()))
     return m
 
 

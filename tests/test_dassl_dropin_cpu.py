@@ -32,3 +32,6 @@ def test_dropin_trains_and_tests_under_real_dassl_like_the_reference(trainer):
     assert all(k.startswith("prompt_learner.ZS_image_encoder.") for k in m["ckpt_keys_missing_in_ours"]), m
     assert m["ours_loaded_ref_ckpt_maxabs"] == 0.0 and m["ref_loaded_our_ckpt_maxabs"] < 1e-5, m
     assert m["acc_after_cross_load"] == m["acc_ref"], m
+    # the on-device input pipeline is opt-in: by default Dassl's DataManager is built exactly as the reference builds it
+    assert m["default_datamanager_kwargs"] == [] and m["device_input_transforms"] and m["device_input_loader_attrs"], m
+    assert len(m["device_input_norm"]) == 3, m

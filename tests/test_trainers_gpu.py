@@ -111,3 +111,59 @@ def test_text_prefix_enqueued_ahead_is_exact_and_invalidated_by_outside_edits():
     assert m["loss_jump_after_edit"] > 0.0, m
     assert m["staged_steps_used"] and m["lookahead_losses_distinct"], m
     assert m["lookahead_param_maxabs"] == 0.0 and m["lookahead_loss_maxabs"] == 0.0, m
+
+
+@pytest.mark.parametrize("name", ["PromptSRC", "CoCoOp"])
+def test_trainer_fed_by_the_device_input_pipeline_equals_the_fp32_fed_trainer(name):
+    """SURVEY 8f-4 through the drop-in: batches collated from `input_pipeline.DeviceTransform` items (what Dassl's
+    DataManager delivers under TRAINER.B200.DEVICE_INPUT) go through `forward_backward` -- uint8 windows over PCIe,
+    `psrc_crop_resize_normalize`, graph replay, look-ahead staging of the next batch -- and through `model_inference`
+    with a different (test) batch size.  The fp32-fed twin receives the very images that kernel produces, so losses,
+    parameters and test logits must agree to the last bit; the kernel's parity with Dassl's PIL chain is
+    test_input_pipeline_gpu.py's subject."""
+    _need_gpu()
+    from torch.utils.data import default_collate
+    from input_ref import synthetic_image
+    from psrc_b200 import input_pipeline as IP, ops
+    from psrc_b200.trainers import LookaheadLoader
+    R, canvas = 64, (96, 96)
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+
+    def u8_batch(n, seed, is_train):
+        torch.manual_seed(seed)
+        tf = IP.DeviceTransform(size=R, is_train=is_train, canvas=canvas)
+        items = [tf(synthetic_image(70 + 9 * k, 120 - 7 * k, seed + k)) for k in range(n)]       # some exceed the canvas
+        lab = torch.randint(0, len(TC.NAME_LENS), (n,), generator=torch.Generator().manual_seed(seed))
+        return {"img": default_collate(items), "label": lab}
+
+    def as_fp32(b):
+        it, out = b["img"], torch.empty(b["label"].shape[0], 3, R, R, device="cuda")
+        ops.crop_resize_normalize(it["u8"].cuda(), it["geom_f"].cuda(), it["geom_i"].cuda(), out, 1, 2,
+                                  IP.max_taps(it["geom_f"].numpy(), 1), mean, std)
+        torch.cuda.synchronize()
+        return {"img": out.cpu(), "label": b["label"]}
+
+    train = [u8_batch(TC.B, 10 * s, True) for s in range(4)]
+    test = u8_batch(5, 99, False)
+    out = {}
+    for feed in ("u8", "fp32"):
+        torch.manual_seed(1234)                            # CoCoOp's meta-net is randomly initialised at build time
+        tr, cfg, _ = TC.make_trainer(name, "fp32")
+        tr.model.input_kwargs = {"interpolation": "bicubic", "mean": mean, "std": std}
+        batches = train if feed == "u8" else [as_fp32(b) for b in train]
+        losses = []
+        for b in LookaheadLoader(batches):                 # step 2 onwards replays the captured graph
+            tr.batch_idx = 0
+            losses.append(tr.forward_backward(b)["loss"])
+        tr.set_model_mode("eval")
+        with torch.no_grad():
+            tb = test if feed == "u8" else as_fp32(test)
+            inp, _ = tr.parse_batch_test({"img": tb["img"], "label": tb["label"]})
+            logits = tr.model_inference(inp).float().cpu()
+        out[feed] = (losses, tr.model._step.flat_param.clone(), logits,
+                     getattr(tr.model._step, "_graph", None) is not None)
+    (l_u, p_u, g_u, cap_u), (l_f, p_f, g_f, _) = out["u8"], out["fp32"]
+    assert cap_u, "the u8-fed trainer must reach the captured-graph path"
+    assert l_u == l_f, (l_u, l_f)
+    assert torch.equal(p_u, p_f) and torch.equal(g_u, g_f)
+    assert g_u.shape == (5, len(TC.NAME_LENS)) and all(torch.isfinite(torch.tensor(l_u)))
