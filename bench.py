@@ -528,7 +528,7 @@ def gemm_roofline(torch, ops, dev, shapes, peaks, ms_dev):
     return {"bound": "tensor", "kernel": "pair::gemm_pair_kernel (tcgen05.mma.cta_group::2 + TMA + TMEM)",
             "achieved": round(ach, 1), "peak": peaks["tf_burst"], "unit": "TFLOP/s",
             "frac": round(ach / peaks["tf_burst"], 4),
-            "peak_source": peaks["source"] + ", burst bf16 (kernel timed alone)", "traffic": gemm_traffic(),
+            "peak_source": peaks["source"] + ", burst bf16 (kernel timed alone; 20 back-to-back launches per shape on the same operands = warm L2)", "traffic": gemm_traffic(),
             "launches_per_step": n_launch, "avg_launch_us": round(tot_ms / n_launch * 1e3, 2),
             "gemm_share_of_step": round(tot_ms / ms_dev, 3),
             "cublas_same_shapes": None if cublas_ms == 0 else {
